@@ -1,0 +1,197 @@
+// api.cu -- LEVEL 0 (queries) and LEVEL 1 (raw launchers) of include/b200_stream.h.
+#include <atomic>
+#include <limits.h>
+#include <mutex>
+#include <stdio.h>
+#include <string.h>
+
+#include "internal.h"
+#include "kernels.cuh"
+
+namespace b200 {
+
+static std::atomic<uint64_t> g_launches{0};
+void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int cuda_fail(cudaError_t e, const char* expr, const char* file, int line) {
+  // same information as the reference's CU() macro prints (src/cuda/CUDAStream.cu:14-17)
+  set_error("CUDA Error at %s:%d: %s (%d)\n  %s", file, line, cudaGetErrorString(e), (int)e, expr);
+  if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver || e == cudaErrorInvalidDevice) return B200_ENODEVICE;
+  if (e == cudaErrorMemoryAllocation) return B200_ENOMEM;
+  return B200_ECUDA;
+}
+
+static const int kMaxDevices = 64;
+static DeviceProps g_props[kMaxDevices];
+static std::atomic<int> g_props_ready[kMaxDevices];
+static std::mutex g_props_mu;
+
+static int load_props(int dev) {
+  std::lock_guard<std::mutex> lock(g_props_mu);
+  if (g_props_ready[dev].load(std::memory_order_acquire)) return B200_OK;
+  DeviceProps p;
+  B200_CUDA(cudaDeviceGetAttribute(&p.num_sms, cudaDevAttrMultiProcessorCount, dev));
+  B200_CUDA(cudaDeviceGetAttribute(&p.l2_bytes, cudaDevAttrL2CacheSize, dev));
+  B200_CUDA(cudaDeviceGetAttribute(&p.cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+  B200_CUDA(cudaDeviceGetAttribute(&p.cc_minor, cudaDevAttrComputeCapabilityMinor, dev));
+  B200_CUDA(cudaDeviceGetAttribute(&p.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  if (p.cc_major != 10) {
+    // the fatbin holds sm_100a code only: fail loudly instead of hitting "no kernel image"
+    set_error("device %d is compute capability %d.%d; libb200stream is built for sm_100a (B200) only", dev,
+              p.cc_major, p.cc_minor);
+    return B200_EUNSUPPORTED;
+  }
+  g_props[dev] = p;
+  g_props_ready[dev].store(1, std::memory_order_release);
+  return B200_OK;
+}
+
+const DeviceProps* current_device_props(int* device_out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { cuda_fail(e, "cudaGetDevice(&dev)", __FILE__, __LINE__); return nullptr; }
+  if (dev < 0 || dev >= kMaxDevices) { set_error("device index %d out of range", dev); return nullptr; }
+  if (!g_props_ready[dev].load(std::memory_order_acquire) && load_props(dev) != B200_OK) return nullptr;
+  if (device_out) *device_out = dev;
+  return &g_props[dev];
+}
+
+static int check_common(size_t n, int elem_bytes) {
+  (void)n;
+  if (elem_bytes != 4 && elem_bytes != 8) { set_error("elem_bytes must be 4 (float) or 8 (double), got %d", elem_bytes); return B200_EINVAL; }
+  return B200_OK;
+}
+
+// shared body of the six elementwise launchers
+static int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1, double s2,
+                     const b200_launch_cfg* cfg, void* stream) {
+  if (int rc = check_common(n, elem_bytes)) return rc;
+  const bool need_a = kernel != B200_MUL, need_b = kernel != B200_COPY, need_c = true;  // which arrays the op touches
+  if (n > 0 && ((need_a && !a) || (need_b && !b) || (need_c && !c))) { set_error("null array pointer"); return B200_EINVAL; }
+  const DeviceProps* props = current_device_props(nullptr);
+  if (!props) return B200_ENODEVICE;
+  EwCall call;
+  if (int rc = resolve_cfg(kernel, n, elem_bytes, props->num_sms, props->l2_bytes, cfg, &call.r)) return rc;
+  if (n == 0) return B200_OK;
+  call.a = a; call.b = b; call.c = c; call.n = n; call.elem_bytes = elem_bytes;
+  call.s0 = s0; call.s1 = s1; call.s2 = s2;
+  call.stream = static_cast<cudaStream_t>(stream);
+
+  if (kernel == B200_COPY && call.r.variant != B200_VARIANT_LDST) {
+    const size_t bytes = n * (size_t)elem_bytes;
+    if (((uintptr_t)a | (uintptr_t)c) & 15) {
+      // the async-proxy paths need 16-byte alignment: fall through to the register path
+    } else if (call.r.variant == B200_VARIANT_BULK) {
+      return launch_copy_bulk(a, c, bytes, call.r, *props, call.stream);
+    } else {
+      return launch_copy_tma(a, c, bytes, call.r, *props, call.stream);
+    }
+  }
+  call.g = make_geometry(need_a ? a : nullptr, need_b ? b : nullptr, c, n, elem_bytes, call.r.vec_bytes, call.r.block,
+                         call.r.unroll, call.r.cache_hint);
+  call.grid = grid_for(call.r.grid_policy, call.g.ntiles, props->num_sms);
+  switch (kernel) {
+    case B200_INIT: return launch_ew_init(call);
+    case B200_COPY: return launch_ew_copy(call);
+    case B200_MUL: return launch_ew_mul(call);
+    case B200_ADD: return launch_ew_add(call);
+    case B200_TRIAD: return launch_ew_triad(call);
+    case B200_NSTREAM: return launch_ew_nstream(call);
+  }
+  set_error("not an elementwise kernel: %d", kernel);
+  return B200_EINVAL;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+const char* b200_version(void) { return "b200-stream 0.1 (sm_100a; variant of BabelStream 5.0)"; }
+
+uint64_t b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int b200_device_count(void) {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) { (void)cudaGetLastError(); return 0; }
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount(&count)", __FILE__, __LINE__);
+  return count;
+}
+
+int b200_device_name(int device, char* buf, int buflen) {
+  if (!buf || buflen <= 0) { set_error("b200_device_name: no buffer"); return B200_EINVAL; }
+  cudaDeviceProp p;
+  B200_CUDA(cudaGetDeviceProperties(&p, device));
+  snprintf(buf, (size_t)buflen, "%s", p.name);
+  return B200_OK;
+}
+
+int b200_driver_version(int device) {
+  (void)device;
+  int v = 0;
+  B200_CUDA(cudaDriverGetVersion(&v));
+  return v;
+}
+
+int b200_device_info(int device, int* num_sms, int* cc_major, int* cc_minor, size_t* total_mem, int* l2_bytes,
+                     int* mem_clock_khz, int* mem_bus_bits) {
+  int v;
+  if (num_sms) { B200_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device)); *num_sms = v; }
+  if (cc_major) { B200_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMajor, device)); *cc_major = v; }
+  if (cc_minor) { B200_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMinor, device)); *cc_minor = v; }
+  if (l2_bytes) { B200_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrL2CacheSize, device)); *l2_bytes = v; }
+  if (mem_clock_khz) { B200_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMemoryClockRate, device)); *mem_clock_khz = v; }
+  if (mem_bus_bits) { B200_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrGlobalMemoryBusWidth, device)); *mem_bus_bits = v; }
+  if (total_mem) {
+    cudaDeviceProp p;
+    B200_CUDA(cudaGetDeviceProperties(&p, device));
+    *total_mem = p.totalGlobalMem;
+  }
+  return B200_OK;
+}
+
+int b200_launch_init(void* a, void* b, void* c, size_t n, int elem_bytes, double ia, double ib, double ic,
+                     const b200_launch_cfg* cfg, void* stream) {
+  return launch_ew(B200_INIT, a, b, c, n, elem_bytes, ia, ib, ic, cfg, stream);
+}
+int b200_launch_copy(const void* a, void* c, size_t n, int elem_bytes, const b200_launch_cfg* cfg, void* stream) {
+  return launch_ew(B200_COPY, const_cast<void*>(a), nullptr, c, n, elem_bytes, 0, 0, 0, cfg, stream);
+}
+int b200_launch_mul(void* b, const void* c, size_t n, int elem_bytes, double scalar, const b200_launch_cfg* cfg,
+                    void* stream) {
+  return launch_ew(B200_MUL, nullptr, b, const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, stream);
+}
+int b200_launch_add(const void* a, const void* b, void* c, size_t n, int elem_bytes, const b200_launch_cfg* cfg,
+                    void* stream) {
+  return launch_ew(B200_ADD, const_cast<void*>(a), const_cast<void*>(b), c, n, elem_bytes, 0, 0, 0, cfg, stream);
+}
+int b200_launch_triad(void* a, const void* b, const void* c, size_t n, int elem_bytes, double scalar,
+                      const b200_launch_cfg* cfg, void* stream) {
+  return launch_ew(B200_TRIAD, a, const_cast<void*>(b), const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, stream);
+}
+int b200_launch_nstream(void* a, const void* b, const void* c, size_t n, int elem_bytes, double scalar,
+                        const b200_launch_cfg* cfg, void* stream) {
+  return launch_ew(B200_NSTREAM, a, const_cast<void*>(b), const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, stream);
+}
+
+size_t b200_dot_workspace_bytes(void) { return kDotWorkspaceBytes; }
+
+int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                    void* result_host_mapped, const b200_launch_cfg* cfg, void* stream) {
+  if (int rc = check_common(n, elem_bytes)) return rc;
+  if (!workspace || (n > 0 && (!a || !b))) { set_error("b200_launch_dot: null pointer"); return B200_EINVAL; }
+  const DeviceProps* props = current_device_props(nullptr);
+  if (!props) return B200_ENODEVICE;
+  DotCall call;
+  if (int rc = resolve_cfg(B200_DOT, n, elem_bytes, props->num_sms, props->l2_bytes, cfg, &call.r)) return rc;
+  call.a = a; call.b = b; call.n = n; call.elem_bytes = elem_bytes;
+  call.workspace = workspace; call.result_dev = result_dev; call.result_host = result_host_mapped;
+  call.stream = static_cast<cudaStream_t>(stream);
+  call.g = make_geometry(a, b, nullptr, n, elem_bytes, call.r.vec_bytes, call.r.block, call.r.unroll, call.r.cache_hint);
+  call.grid = grid_for(call.r.grid_policy, call.g.ntiles, props->num_sms);
+  return launch_dot_impl(call);
+}
+
+}  // extern "C"

@@ -1,0 +1,605 @@
+// context.cu -- LEVEL 2 of include/b200_stream.h: the Stream<T> object.
+//
+// Three device-resident arrays of n elements, sharded contiguously over G GPUs of one box
+// (b200_shard_range).  Every public call is blocking, as src/Stream.h:36 demands.
+//   G == 1 : the caller's thread launches and waits; no helper threads at all.
+//   G  > 1 : one pinned worker thread per GPU, released by a shared sequence number and joined by
+//            spinning on per-worker counters, so that the G launches start together instead of
+//            one after another from a single thread (SURVEY.md section 7 "launch skew").
+// The elementwise kernels never communicate.  dot is the one exchange step: each GPU reduces its
+// shard to one T, and the G values are combined by ONE ncclAllReduce over NVLink (count = 1).
+#include <dlfcn.h>
+#include <nccl.h>  // types only: the library is dlopen'ed, so single-GPU use needs no NCCL at all
+
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
+#include <new>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <thread>
+#include <vector>
+
+#if defined(__x86_64__)
+#include <immintrin.h>
+#define B200_PAUSE() _mm_pause()
+#else
+#define B200_PAUSE() do { } while (0)
+#endif
+
+#include "internal.h"
+#include "kernels.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------
+// NCCL, resolved at run time
+// ---------------------------------------------------------------------------------------------
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  ncclResult_t (*GetVersion)(int*) = nullptr;
+
+  int load() {
+    if (handle) return B200_OK;
+    const char* env = getenv("BABELSTREAM_B200_NCCL_LIB");
+    const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+      if (!nm || !*nm) continue;
+      handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+      if (handle) break;
+    }
+    if (!handle) { set_error("cannot load NCCL (libnccl.so.2): %s", dlerror()); return B200_ENCCL; }
+    CommInitAll = (decltype(CommInitAll))dlsym(handle, "ncclCommInitAll");
+    CommDestroy = (decltype(CommDestroy))dlsym(handle, "ncclCommDestroy");
+    AllReduce = (decltype(AllReduce))dlsym(handle, "ncclAllReduce");
+    GetErrorString = (decltype(GetErrorString))dlsym(handle, "ncclGetErrorString");
+    GetVersion = (decltype(GetVersion))dlsym(handle, "ncclGetVersion");
+    if (!CommInitAll || !CommDestroy || !AllReduce || !GetErrorString) {
+      set_error("libnccl is missing a required symbol");
+      return B200_ENCCL;
+    }
+    return B200_OK;
+  }
+};
+
+enum { CMD_NONE = 0, CMD_KERNEL, CMD_READ, CMD_WRITE, CMD_QUIT };
+enum { COMBINE_NCCL = 0, COMBINE_HOST = 1 };
+enum { SYNC_STREAM = 0, SYNC_SPIN = 1 };
+
+struct Shard {
+  int dev = 0;
+  size_t begin = 0, count = 0;
+  cudaStream_t stream = nullptr;
+  void *a = nullptr, *b = nullptr, *c = nullptr;
+  void* dot_ws = nullptr;        // partials + ticket
+  void* dot_dev = nullptr;       // 2 x 8 bytes: [0] this GPU's partial, [1] all-reduced value
+  void* dot_host = nullptr;      // mapped pinned, 8 bytes
+  void* dot_host_dev = nullptr;  // device-side alias of dot_host
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  ncclComm_t comm = nullptr;
+  float last_ms = -1.f;
+  int status = B200_OK;
+  std::string error;
+  std::atomic<uint64_t> done{0};
+};
+
+struct Command {
+  int kind = CMD_NONE;
+  int kernel = 0;
+  double s0 = 0, s1 = 0, s2 = 0;
+  void* host[3] = {nullptr, nullptr, nullptr};  // read: destinations; write: sources
+};
+
+}  // namespace b200
+
+using namespace b200;
+
+struct b200_ctx {
+  int first_device = 0, ngpus = 1;
+  size_t n = 0;
+  int elem_bytes = 8;
+  std::vector<Shard*> shards;
+
+  // options
+  b200_launch_cfg tune[B200_NUM_KERNELS];
+  bool timing = false;
+  int sync_mode = SYNC_STREAM;
+  int combine = COMBINE_NCCL;
+  NcclApi nccl;
+  bool nccl_ready = false;
+
+  // host mirrors for get_arrays
+  void* host[3] = {nullptr, nullptr, nullptr};
+  bool host_pinned = false;
+
+  // workers (ngpus > 1)
+  std::vector<std::thread> workers;
+  Command cmd;
+  std::atomic<uint64_t> seq{0};
+  std::atomic<int> sleepers{0};
+  std::mutex mu;
+  std::condition_variable cv;
+};
+
+namespace b200 {
+
+static int stream_wait(b200_ctx* ctx, Shard* s) {
+  if (ctx->sync_mode == SYNC_SPIN) {
+    for (;;) {
+      cudaError_t e = cudaStreamQuery(s->stream);
+      if (e == cudaSuccess) return B200_OK;
+      if (e != cudaErrorNotReady) return cuda_fail(e, "cudaStreamQuery(stream)", __FILE__, __LINE__);
+      B200_PAUSE();
+    }
+  }
+  B200_CUDA(cudaStreamSynchronize(s->stream));
+  return B200_OK;
+}
+
+// Launch one kernel on one shard (device already current).  No synchronisation.
+static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd) {
+  const int eb = ctx->elem_bytes;
+  const b200_launch_cfg* cfg = &ctx->tune[cmd.kernel];
+  void* st = s->stream;
+  if (cmd.kernel == B200_DOT) {
+    const bool single = ctx->ngpus == 1;
+    // single GPU: the kernel writes the sum straight into mapped host memory (zero-copy)
+    if (s->count == 0) {
+      B200_CUDA(cudaMemsetAsync(s->dot_dev, 0, 8, s->stream));
+      if (single || ctx->combine == COMBINE_HOST) memset(s->dot_host, 0, 8);
+      return B200_OK;
+    }
+    const bool to_host = single || ctx->combine == COMBINE_HOST;
+    return b200_launch_dot(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, to_host ? s->dot_host_dev : nullptr, cfg, st);
+  }
+  if (s->count == 0) return B200_OK;
+  switch (cmd.kernel) {
+    case B200_INIT: return b200_launch_init(s->a, s->b, s->c, s->count, eb, cmd.s0, cmd.s1, cmd.s2, cfg, st);
+    case B200_COPY: return b200_launch_copy(s->a, s->c, s->count, eb, cfg, st);
+    case B200_MUL: return b200_launch_mul(s->b, s->c, s->count, eb, cmd.s0, cfg, st);
+    case B200_ADD: return b200_launch_add(s->a, s->b, s->c, s->count, eb, cfg, st);
+    case B200_TRIAD: return b200_launch_triad(s->a, s->b, s->c, s->count, eb, cmd.s0, cfg, st);
+    case B200_NSTREAM: return b200_launch_nstream(s->a, s->b, s->c, s->count, eb, cmd.s0, cfg, st);
+  }
+  set_error("unknown kernel id %d", cmd.kernel);
+  return B200_EINVAL;
+}
+
+// Everything one GPU does for one command, including the wait.  Runs on the worker thread of the
+// shard (G > 1) or on the caller's thread (G == 1).
+static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
+  Shard* s = ctx->shards[g];
+  const size_t eb = (size_t)ctx->elem_bytes;
+  // G == 1 runs on the caller's thread, whose current device may have been changed since create
+  if (ctx->ngpus == 1) B200_CUDA(cudaSetDevice(s->dev));
+  if (cmd.kind == CMD_KERNEL) {
+    if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev0, s->stream));
+    if (int rc = shard_launch(ctx, s, cmd)) return rc;
+    if (cmd.kernel == B200_DOT && ctx->ngpus > 1 && ctx->combine == COMBINE_NCCL) {
+      // the one collective of the whole benchmark: G partial sums -> every GPU holds the total
+      char* buf = static_cast<char*>(s->dot_dev);
+      ncclResult_t r = ctx->nccl.AllReduce(buf, buf + 8, 1, eb == 8 ? ncclDouble : ncclFloat, ncclSum, s->comm, s->stream);
+      if (r != ncclSuccess) { set_error("ncclAllReduce failed: %s", ctx->nccl.GetErrorString(r)); return B200_ENCCL; }
+      if (g == 0) B200_CUDA(cudaMemcpyAsync(s->dot_host, buf + 8, eb, cudaMemcpyDeviceToHost, s->stream));
+    }
+    if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev1, s->stream));
+    if (int rc = stream_wait(ctx, s)) return rc;
+    if (ctx->timing) B200_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
+    return B200_OK;
+  }
+  if (cmd.kind == CMD_READ || cmd.kind == CMD_WRITE) {
+    void* dev[3] = {s->a, s->b, s->c};
+    for (int k = 0; k < 3; k++) {
+      if (!cmd.host[k] || s->count == 0) continue;
+      char* h = static_cast<char*>(cmd.host[k]) + s->begin * eb;
+      if (cmd.kind == CMD_READ) B200_CUDA(cudaMemcpyAsync(h, dev[k], s->count * eb, cudaMemcpyDeviceToHost, s->stream));
+      else B200_CUDA(cudaMemcpyAsync(dev[k], h, s->count * eb, cudaMemcpyHostToDevice, s->stream));
+    }
+    B200_CUDA(cudaStreamSynchronize(s->stream));
+    return B200_OK;
+  }
+  return B200_OK;
+}
+
+static void worker_main(b200_ctx* ctx, int g) {
+  Shard* s = ctx->shards[g];
+  cudaSetDevice(s->dev);
+  uint64_t seen = 0;
+  for (;;) {
+    // spin briefly (the benchmark issues calls back to back), then sleep on the condition variable
+    int spins = 0;
+    while (ctx->seq.load(std::memory_order_acquire) == seen) {
+      if (++spins < (1 << 16)) { B200_PAUSE(); continue; }
+      std::unique_lock<std::mutex> lock(ctx->mu);
+      ctx->sleepers.fetch_add(1);
+      ctx->cv.wait(lock, [&] { return ctx->seq.load() != seen; });
+      ctx->sleepers.fetch_sub(1);
+    }
+    seen++;
+    const Command cmd = ctx->cmd;  // published before seq was bumped
+    if (cmd.kind == CMD_QUIT) { s->done.store(seen, std::memory_order_release); return; }
+    const int rc = shard_execute(ctx, g, cmd);
+    s->status = rc;
+    if (rc != B200_OK) s->error = b200_last_error();
+    s->done.store(seen, std::memory_order_release);
+  }
+}
+
+// Run one command on every shard and wait for all of them.
+static int run_all(b200_ctx* ctx, const Command& cmd) {
+  if (ctx->ngpus == 1) return shard_execute(ctx, 0, cmd);
+  ctx->cmd = cmd;
+  const uint64_t target = ctx->seq.fetch_add(1, std::memory_order_seq_cst) + 1;
+  if (ctx->sleepers.load(std::memory_order_seq_cst) > 0) {
+    { std::lock_guard<std::mutex> lock(ctx->mu); }
+    ctx->cv.notify_all();
+  }
+  int rc = B200_OK;
+  for (Shard* s : ctx->shards) {
+    unsigned spins = 0;
+    while (s->done.load(std::memory_order_acquire) < target) {
+      if (++spins < (1u << 20)) B200_PAUSE();
+      else std::this_thread::yield();
+    }
+    if (s->status != B200_OK && rc == B200_OK) { rc = s->status; set_error("GPU %d: %s", s->dev, s->error.c_str()); }
+  }
+  return rc;
+}
+
+static void parse_cfg_fields(b200_launch_cfg* c, const std::string& fields) {
+  // "vec=32,unroll=2,block=256,grid=-4,hint=3,variant=2,stages=4,chunk=32768,contract=1"
+  size_t pos = 0;
+  while (pos < fields.size()) {
+    size_t end = fields.find(',', pos);
+    if (end == std::string::npos) end = fields.size();
+    const std::string kv = fields.substr(pos, end - pos);
+    const size_t eq = kv.find('=');
+    if (eq != std::string::npos) {
+      const std::string k = kv.substr(0, eq);
+      const int v = atoi(kv.c_str() + eq + 1);
+      if (k == "vec") c->vec_bytes = v; else if (k == "unroll") c->unroll = v; else if (k == "block") c->block = v;
+      else if (k == "grid") c->grid = v; else if (k == "hint") c->cache_hint = v; else if (k == "variant") c->variant = v;
+      else if (k == "stages") c->stages = v; else if (k == "chunk") c->chunk_bytes = v; else if (k == "contract") c->contract = v;
+    }
+    pos = end + 1;
+  }
+}
+
+static int kernel_by_name(const std::string& s) {
+  const char* names[B200_NUM_KERNELS] = {"copy", "mul", "add", "triad", "nstream", "dot", "init"};
+  for (int i = 0; i < B200_NUM_KERNELS; i++) if (s == names[i]) return i;
+  return -1;
+}
+
+static int apply_option(b200_ctx* ctx, const std::string& key, const std::string& val) {
+  if (key == "contract") {
+    const int c = (val == "off" || val == "0" || val == "unfused") ? 2 : 1;
+    for (auto& t : ctx->tune) t.contract = c;
+  } else if (key == "copy_variant") {
+    int v = val == "ldst" ? B200_VARIANT_LDST : val == "bulk" ? B200_VARIANT_BULK : val == "tma" ? B200_VARIANT_TMA : B200_VARIANT_AUTO;
+    ctx->tune[B200_COPY].variant = v;
+  } else if (key == "dot_variant") {
+    ctx->tune[B200_DOT].variant = val == "two_pass" ? B200_VARIANT_DOT_TWO_PASS : val == "ticket" ? B200_VARIANT_DOT_TICKET : 0;
+  } else if (key == "dot_combine") {
+    ctx->combine = val == "host" ? COMBINE_HOST : COMBINE_NCCL;
+  } else if (key == "timing") {
+    ctx->timing = (val == "1" || val == "on" || val == "true");
+  } else if (key == "sync") {
+    ctx->sync_mode = val == "spin" ? SYNC_SPIN : SYNC_STREAM;
+  } else if (key == "tune") {
+    // "<kernel>:<fields>;<kernel>:<fields>"   kernel "all" applies to the six elementwise kernels
+    size_t pos = 0;
+    while (pos < val.size()) {
+      size_t end = val.find(';', pos);
+      if (end == std::string::npos) end = val.size();
+      const std::string item = val.substr(pos, end - pos);
+      const size_t colon = item.find(':');
+      if (colon != std::string::npos) {
+        const std::string kn = item.substr(0, colon), fields = item.substr(colon + 1);
+        if (kn == "all") { for (int k = 0; k < B200_NUM_KERNELS; k++) if (k != B200_DOT) parse_cfg_fields(&ctx->tune[k], fields); }
+        else {
+          const int k = kernel_by_name(kn);
+          if (k < 0) { set_error("tune: unknown kernel '%s'", kn.c_str()); return B200_EINVAL; }
+          parse_cfg_fields(&ctx->tune[k], fields);
+        }
+      }
+      pos = end + 1;
+    }
+  } else {
+    set_error("unknown option '%s'", key.c_str());
+    return B200_EINVAL;
+  }
+  return B200_OK;
+}
+
+static void free_host_mirrors(b200_ctx* ctx) {
+  for (auto& h : ctx->host) {
+    if (!h) continue;
+    if (ctx->host_pinned) cudaFreeHost(h); else free(h);
+    h = nullptr;
+  }
+}
+
+static int ensure_host_mirrors(b200_ctx* ctx) {
+  if (ctx->host[0]) return B200_OK;
+  const size_t bytes = ctx->n * (size_t)ctx->elem_bytes;
+  // pinned while it is reasonable (D2H at full PCIe speed); beyond the limit fall back to pageable
+  // memory like the reference's std::vector (CUDAStream.cu:225-233) instead of pinning > 1/3 of RAM
+  double limit_gb = 24.0;
+  if (const char* e = getenv("BABELSTREAM_B200_PINNED_LIMIT_GB")) limit_gb = atof(e);
+  bool pinned = 3.0 * (double)bytes <= limit_gb * 1e9;
+  if (pinned) {
+    for (auto& h : ctx->host) {
+      if (cudaHostAlloc(&h, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) { (void)cudaGetLastError(); h = nullptr; pinned = false; break; }
+    }
+    if (!pinned) { ctx->host_pinned = true; free_host_mirrors(ctx); }
+  }
+  if (!pinned) {
+    for (auto& h : ctx->host) {
+      h = aligned_alloc(2 * 1024 * 1024, ((bytes ? bytes : 1) + (2u << 20) - 1) / (2u << 20) * (2u << 20));
+      if (!h) { set_error("cannot allocate %zu bytes of host memory for get_arrays", bytes); return B200_ENOMEM; }
+    }
+  }
+  ctx->host_pinned = pinned;
+  return B200_OK;
+}
+
+}  // namespace b200
+
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+void b200_destroy(b200_ctx* ctx) {
+  if (!ctx) return;
+  if (!ctx->workers.empty()) {
+    Command q; q.kind = CMD_QUIT;
+    ctx->cmd = q;
+    ctx->seq.fetch_add(1);
+    { std::lock_guard<std::mutex> lock(ctx->mu); }
+    ctx->cv.notify_all();
+    for (auto& t : ctx->workers) t.join();
+  }
+  for (Shard* s : ctx->shards) {
+    if (!s) continue;
+    cudaSetDevice(s->dev);
+    if (s->comm && ctx->nccl.CommDestroy) ctx->nccl.CommDestroy(s->comm);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); cudaFree(s->dot_ws); cudaFree(s->dot_dev);
+    if (s->dot_host) cudaFreeHost(s->dot_host);
+    delete s;
+  }
+  free_host_mirrors(ctx);
+  if (!ctx->shards.empty()) cudaSetDevice(ctx->first_device);
+  delete ctx;
+}
+
+b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int* status) {
+  int rc = B200_OK;
+  b200_ctx* ctx = nullptr;
+  auto fail = [&](int code) -> b200_ctx* {
+    if (status) *status = code;
+    const std::string keep = b200_last_error();  // destroy may overwrite it
+    b200_destroy(ctx);
+    set_error("%s", keep.c_str());
+    return nullptr;
+  };
+  if (elem_bytes != 4 && elem_bytes != 8) { set_error("elem_bytes must be 4 or 8, got %d", elem_bytes); return fail(B200_EINVAL); }
+  if (ngpus == 0) {
+    const char* e = getenv("BABELSTREAM_B200_NGPUS");
+    ngpus = e ? atoi(e) : 1;
+  }
+  const int count = b200_device_count();
+  if (count <= 0) { set_error("no CUDA device available: libb200stream has no CPU fallback"); return fail(B200_ENODEVICE); }
+  if (ngpus < 1 || first_device < 0 || first_device + ngpus > count) {
+    // the reference throws std::runtime_error("Invalid device index") here, CUDAStream.cu:87-88
+    set_error("Invalid device index: devices %d..%d requested, %d present", first_device, first_device + ngpus - 1, count);
+    return fail(B200_ENODEVICE);
+  }
+  ctx = new (std::nothrow) b200_ctx;
+  if (!ctx) { set_error("out of host memory"); return fail(B200_ENOMEM); }
+  ctx->first_device = first_device; ctx->ngpus = ngpus; ctx->n = n; ctx->elem_bytes = elem_bytes;
+  memset(ctx->tune, 0, sizeof ctx->tune);
+
+  // options from the environment: BABELSTREAM_B200_<KEY>
+  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune"};
+  for (const char* k : keys) {
+    std::string env = "BABELSTREAM_B200_";
+    for (const char* p = k; *p; p++) env += (char)toupper(*p);
+    if (const char* v = getenv(env.c_str())) { rc = apply_option(ctx, k, v); if (rc) return fail(rc); }
+  }
+
+  for (int g = 0; g < ngpus; g++) {
+    Shard* s = new (std::nothrow) Shard;
+    if (!s) { set_error("out of host memory"); return fail(B200_ENOMEM); }
+    ctx->shards.push_back(s);
+    s->dev = first_device + g;
+    b200_shard_range(n, elem_bytes, ngpus, g, &s->begin, &s->count);
+    auto cu = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && rc == B200_OK) rc = cuda_fail(e, what, __FILE__, __LINE__); };
+    cu(cudaSetDevice(s->dev), "cudaSetDevice");
+    if (rc) return fail(rc);
+    (void)cudaSetDeviceFlags(cudaDeviceScheduleSpin);  // best effort: blocking calls should not yield the core
+    (void)cudaGetLastError();
+    if (!current_device_props(nullptr)) return fail(B200_EUNSUPPORTED);
+    size_t free_b = 0, total_b = 0;
+    cu(cudaMemGetInfo(&free_b, &total_b), "cudaMemGetInfo");
+    const size_t shard_bytes = s->count * (size_t)elem_bytes;
+    if (rc == B200_OK && 3.0 * (double)shard_bytes + 1e6 > (double)free_b) {
+      // reference: "Device does not have enough memory for all buffers", CUDAStream.cu:135-139
+      set_error("Device does not have enough memory for all buffers: %.3f GB requested on GPU %d, %.3f GB free",
+                3.0 * shard_bytes * 1e-9, s->dev, free_b * 1e-9);
+      return fail(B200_ENOMEM);
+    }
+    cu(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking), "cudaStreamCreateWithFlags");
+    cu(cudaEventCreate(&s->ev0), "cudaEventCreate");
+    cu(cudaEventCreate(&s->ev1), "cudaEventCreate");
+    const size_t alloc = shard_bytes ? shard_bytes : 256;
+    cu(cudaMalloc(&s->a, alloc), "cudaMalloc(a)");
+    cu(cudaMalloc(&s->b, alloc), "cudaMalloc(b)");
+    cu(cudaMalloc(&s->c, alloc), "cudaMalloc(c)");
+    cu(cudaMalloc(&s->dot_ws, kDotWorkspaceBytes), "cudaMalloc(dot workspace)");
+    cu(cudaMalloc(&s->dot_dev, 16), "cudaMalloc(dot scalars)");
+    cu(cudaHostAlloc(&s->dot_host, 8, cudaHostAllocMapped | cudaHostAllocPortable), "cudaHostAlloc(dot result)");
+    if (rc) return fail(rc);
+    cu(cudaHostGetDevicePointer(&s->dot_host_dev, s->dot_host, 0), "cudaHostGetDevicePointer");
+    cu(cudaMemsetAsync(s->dot_ws, 0, kDotWorkspaceBytes, s->stream), "cudaMemsetAsync");
+    cu(cudaMemsetAsync(s->dot_dev, 0, 16, s->stream), "cudaMemsetAsync");
+    cu(cudaStreamSynchronize(s->stream), "cudaStreamSynchronize");
+    if (rc) return fail(rc);
+  }
+
+  if (ngpus > 1) {
+    if (ctx->combine == COMBINE_NCCL) {
+      if ((rc = ctx->nccl.load())) return fail(rc);
+      std::vector<int> devs(ngpus);
+      std::vector<ncclComm_t> comms(ngpus);
+      for (int g = 0; g < ngpus; g++) devs[g] = first_device + g;
+      ncclResult_t r = ctx->nccl.CommInitAll(comms.data(), ngpus, devs.data());
+      if (r != ncclSuccess) { set_error("ncclCommInitAll failed: %s", ctx->nccl.GetErrorString(r)); return fail(B200_ENCCL); }
+      for (int g = 0; g < ngpus; g++) ctx->shards[g]->comm = comms[g];
+      ctx->nccl_ready = true;
+    }
+    for (int g = 0; g < ngpus; g++) ctx->workers.emplace_back(worker_main, ctx, g);
+  }
+  cudaSetDevice(first_device);
+  if (status) *status = B200_OK;
+  return ctx;
+}
+
+int b200_set_option(b200_ctx* ctx, const char* key, const char* value) {
+  if (!ctx || !key || !value) { set_error("b200_set_option: null argument"); return B200_EINVAL; }
+  if (std::string(key) == "dot_combine" && ctx->ngpus > 1 && std::string(value) != "host" && !ctx->nccl_ready) {
+    set_error("dot_combine=nccl must be chosen before b200_create (BABELSTREAM_B200_DOT_COMBINE)");
+    return B200_EINVAL;
+  }
+  return apply_option(ctx, key, value);
+}
+
+int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
+  if (!ctx || !buf || buflen <= 0) { set_error("b200_describe: null argument"); return B200_EINVAL; }
+  const DeviceProps* props = current_device_props(nullptr);
+  if (!props) return B200_ENODEVICE;
+  std::string out;
+  char line[256];
+  snprintf(line, sizeof line, "GPUs: %d (devices %d..%d), %zu elements of %d bytes, shard %zu elements\n", ctx->ngpus,
+           ctx->first_device, ctx->first_device + ctx->ngpus - 1, ctx->n, ctx->elem_bytes, ctx->shards[0]->count);
+  out += line;
+  const char* names[B200_NUM_KERNELS] = {"copy", "mul", "add", "triad", "nstream", "dot", "init"};
+  for (int k = 0; k < B200_NUM_KERNELS; k++) {
+    Resolved r;
+    if (resolve_cfg(k, ctx->shards[0]->count, ctx->elem_bytes, props->num_sms, props->l2_bytes, &ctx->tune[k], &r)) continue;
+    const Geometry g = make_geometry(nullptr, nullptr, nullptr, ctx->shards[0]->count, ctx->elem_bytes, r.vec_bytes, r.block, r.unroll, r.cache_hint);
+    snprintf(line, sizeof line, "  %-8s vec %2dB unroll %d block %4d grid %-9u hint %d variant %d %s\n", names[k], r.vec_bytes,
+             r.unroll, r.block, grid_for(r.grid_policy, g.ntiles, props->num_sms), r.cache_hint, r.variant,
+             r.contract == 2 ? "unfused" : "fused");
+    out += line;
+  }
+  if (ctx->ngpus > 1) {
+    int v = 0;
+    if (ctx->nccl_ready && ctx->nccl.GetVersion) ctx->nccl.GetVersion(&v);
+    snprintf(line, sizeof line, "  dot combine: %s", ctx->combine == COMBINE_NCCL ? "ncclAllReduce(count=1)" : "host sum in rank order");
+    out += line;
+    if (v) { snprintf(line, sizeof line, " (NCCL %d)", v); out += line; }
+    out += "\n";
+  }
+  snprintf(buf, (size_t)buflen, "%s", out.c_str());
+  return B200_OK;
+}
+
+static int run_kernel(b200_ctx* ctx, int kernel, double s0, double s1, double s2) {
+  if (!ctx) { set_error("null context"); return B200_EINVAL; }
+  Command cmd;
+  cmd.kind = CMD_KERNEL; cmd.kernel = kernel; cmd.s0 = s0; cmd.s1 = s1; cmd.s2 = s2;
+  return run_all(ctx, cmd);
+}
+
+int b200_init_arrays(b200_ctx* ctx, double ia, double ib, double ic) { return run_kernel(ctx, B200_INIT, ia, ib, ic); }
+int b200_copy(b200_ctx* ctx) { return run_kernel(ctx, B200_COPY, 0, 0, 0); }
+int b200_mul(b200_ctx* ctx, double scalar) { return run_kernel(ctx, B200_MUL, scalar, 0, 0); }
+int b200_add(b200_ctx* ctx) { return run_kernel(ctx, B200_ADD, 0, 0, 0); }
+int b200_triad(b200_ctx* ctx, double scalar) { return run_kernel(ctx, B200_TRIAD, scalar, 0, 0); }
+int b200_nstream(b200_ctx* ctx, double scalar) { return run_kernel(ctx, B200_NSTREAM, scalar, 0, 0); }
+
+int b200_dot(b200_ctx* ctx, double* result) {
+  if (int rc = run_kernel(ctx, B200_DOT, 0, 0, 0)) return rc;
+  double total;
+  if (ctx->ngpus > 1 && ctx->combine == COMBINE_HOST) {
+    // G values, added in rank order in type T: deterministic
+    if (ctx->elem_bytes == 8) { double t = 0; for (Shard* s : ctx->shards) t += *static_cast<volatile double*>(s->dot_host); total = t; }
+    else { float t = 0; for (Shard* s : ctx->shards) t += *static_cast<volatile float*>(s->dot_host); total = t; }
+  } else {
+    const void* h = ctx->shards[0]->dot_host;
+    total = ctx->elem_bytes == 8 ? *static_cast<const volatile double*>(h) : (double)*static_cast<const volatile float*>(h);
+  }
+  if (result) *result = total;
+  return B200_OK;
+}
+
+int b200_run(b200_ctx* ctx, int kernel, double scalar, double* result) {
+  switch (kernel) {
+    case B200_COPY: return b200_copy(ctx);
+    case B200_MUL: return b200_mul(ctx, scalar);
+    case B200_ADD: return b200_add(ctx);
+    case B200_TRIAD: return b200_triad(ctx, scalar);
+    case B200_NSTREAM: return b200_nstream(ctx, scalar);
+    case B200_DOT: return b200_dot(ctx, result);
+  }
+  set_error("b200_run: kernel id %d is not a benchmark kernel", kernel);
+  return B200_EINVAL;
+}
+
+static int transfer(b200_ctx* ctx, int kind, void* a, void* b, void* c) {
+  if (!ctx) { set_error("null context"); return B200_EINVAL; }
+  Command cmd;
+  cmd.kind = kind; cmd.host[0] = a; cmd.host[1] = b; cmd.host[2] = c;
+  return run_all(ctx, cmd);
+}
+
+int b200_read_arrays(b200_ctx* ctx, void* a, void* b, void* c) { return transfer(ctx, CMD_READ, a, b, c); }
+int b200_write_arrays(b200_ctx* ctx, const void* a, const void* b, const void* c) {
+  return transfer(ctx, CMD_WRITE, const_cast<void*>(a), const_cast<void*>(b), const_cast<void*>(c));
+}
+
+int b200_get_arrays(b200_ctx* ctx, const void** a, const void** b, const void** c) {
+  if (!ctx) { set_error("null context"); return B200_EINVAL; }
+  if (int rc = ensure_host_mirrors(ctx)) return rc;
+  if (int rc = transfer(ctx, CMD_READ, ctx->host[0], ctx->host[1], ctx->host[2])) return rc;
+  if (a) *a = ctx->host[0];
+  if (b) *b = ctx->host[1];
+  if (c) *c = ctx->host[2];
+  return B200_OK;
+}
+
+int b200_num_gpus(b200_ctx* ctx) { return ctx ? ctx->ngpus : B200_EINVAL; }
+size_t b200_array_size(b200_ctx* ctx) { return ctx ? ctx->n : 0; }
+int b200_elem_bytes(b200_ctx* ctx) { return ctx ? ctx->elem_bytes : B200_EINVAL; }
+
+double b200_last_kernel_ms(b200_ctx* ctx) {
+  if (!ctx || !ctx->timing) return -1.0;
+  float ms = -1.f;
+  for (Shard* s : ctx->shards) if (s->last_ms > ms) ms = s->last_ms;
+  return (double)ms;
+}
+
+int b200_shard_info(b200_ctx* ctx, int g, int* device, void** a, void** b, void** c, size_t* begin, size_t* count,
+                    void** stream) {
+  if (!ctx || g < 0 || g >= ctx->ngpus) { set_error("b200_shard_info: bad shard index"); return B200_EINVAL; }
+  Shard* s = ctx->shards[g];
+  if (device) *device = s->dev;
+  if (a) *a = s->a;
+  if (b) *b = s->b;
+  if (c) *c = s->c;
+  if (begin) *begin = s->begin;
+  if (count) *count = s->count;
+  if (stream) *stream = s->stream;
+  return B200_OK;
+}
+
+}  // extern "C"

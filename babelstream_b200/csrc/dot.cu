@@ -1,0 +1,63 @@
+// dot.cu -- launcher for the two dot variants (see kernels.cuh for the algorithm).
+#include "internal.h"
+#include "kernels.cuh"
+
+namespace b200 {
+
+#define B200_DOT_FOR_HINT(H)                                                                      \
+  B200_DOT_CASE(16, 1, H) B200_DOT_CASE(16, 2, H) B200_DOT_CASE(16, 4, H) B200_DOT_CASE(16, 8, H) \
+  B200_DOT_CASE(32, 1, H) B200_DOT_CASE(32, 2, H) B200_DOT_CASE(32, 4, H)
+
+template <typename T, bool FUSED, bool TICKET>
+static int launch_dot_typed(const DotCall& call) {
+  using Kernel = void (*)(const DotArgs);
+  Kernel k = nullptr;
+  const int vb = call.g.vec_bytes, u = call.g.unroll, h = call.g.cache_hint;
+#define B200_DOT_CASE(VB, U, H) \
+  if (vb == VB && u == U && h == H) k = dot_kernel<T, VB, U, H, FUSED, TICKET>;
+  B200_DOT_FOR_HINT(1) B200_DOT_FOR_HINT(2) B200_DOT_FOR_HINT(3) B200_DOT_FOR_HINT(4) B200_DOT_FOR_HINT(5)
+  if (vb == (int)sizeof(T) && u == 4 && h == 1) k = dot_kernel<T, (int)sizeof(T), 4, 1, FUSED, TICKET>;
+#undef B200_DOT_CASE
+  if (!k) {
+    set_error("no dot kernel compiled for vec_bytes=%d unroll=%d cache_hint=%d", vb, u, h);
+    return B200_EUNSUPPORTED;
+  }
+  if (call.r.block > dot_max_block(vb, u)) {
+    set_error("dot: block %d too large for vec_bytes=%d unroll=%d (max %d)", call.r.block, vb, u, dot_max_block(vb, u));
+    return B200_EINVAL;
+  }
+  DotArgs args;
+  args.a = call.a; args.b = call.b;
+  args.partials = call.workspace;
+  args.ticket = reinterpret_cast<unsigned int*>(static_cast<char*>(call.workspace) + kDotMaxBlocks * 8);
+  args.result_dev = call.result_dev; args.result_host = call.result_host;
+  args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
+  k<<<call.grid, call.r.block, 0, call.stream>>>(args);
+  count_launch();
+  B200_CUDA(cudaPeekAtLastError());
+  if (!TICKET) {
+    dot_final_kernel<T><<<1, 1024, 0, call.stream>>>(static_cast<const T*>(call.workspace), call.grid,
+                                                      static_cast<T*>(call.result_dev),
+                                                      static_cast<T*>(call.result_host));
+    count_launch();
+    B200_CUDA(cudaPeekAtLastError());
+  }
+  return B200_OK;
+}
+
+int launch_dot_impl(const DotCall& call) {
+  const bool fused = call.r.contract != 2;
+  const bool ticket = call.r.variant == B200_VARIANT_DOT_TICKET;
+  if (call.grid > (unsigned)kDotMaxBlocks) {
+    set_error("dot grid %u exceeds the workspace capacity of %d blocks", call.grid, kDotMaxBlocks);
+    return B200_EINVAL;
+  }
+  if (call.elem_bytes == 8) {
+    if (fused) return ticket ? launch_dot_typed<double, true, true>(call) : launch_dot_typed<double, true, false>(call);
+    return ticket ? launch_dot_typed<double, false, true>(call) : launch_dot_typed<double, false, false>(call);
+  }
+  if (fused) return ticket ? launch_dot_typed<float, true, true>(call) : launch_dot_typed<float, true, false>(call);
+  return ticket ? launch_dot_typed<float, false, true>(call) : launch_dot_typed<float, false, false>(call);
+}
+
+}  // namespace b200

@@ -1,0 +1,95 @@
+// internal.h -- shared declarations of libb200stream's translation units (not part of the ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/b200_stream.h"
+
+namespace b200 {
+
+// thread-local error message behind b200_last_error()
+void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+int cuda_fail(cudaError_t e, const char* expr, const char* file, int line);  // sets the message, returns B200_ECUDA
+
+#define B200_CUDA(expr)                                                                   \
+  do {                                                                                    \
+    cudaError_t e__ = (expr);                                                             \
+    if (e__ != cudaSuccess) return ::b200::cuda_fail(e__, #expr, __FILE__, __LINE__);     \
+  } while (0)
+
+struct DeviceProps {
+  int num_sms;
+  int l2_bytes;
+  int cc_major, cc_minor;
+  int max_smem_optin;
+};
+// cached per device; returns nullptr (and sets the error) when there is no usable device
+const DeviceProps* current_device_props(int* device_out);
+
+void count_launch(unsigned n = 1);
+
+// A fully resolved launch: no "auto" left.
+struct Resolved {
+  int vec_bytes, unroll, block, cache_hint, variant, contract, stages, chunk_bytes;
+  int grid_policy;  // the cfg.grid convention: >0 exact, <0 per-SM, INT32_MAX one tile per block
+};
+
+// Fills every auto field of `in` (may be null) for (kernel, n, elem_bytes).  Pure host logic.
+int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
+                Resolved* out);
+// grid size for `ntiles` tiles under the policy
+unsigned grid_for(int grid_policy, unsigned long long ntiles, int num_sms);
+
+// Geometry of one vectorised pass over n elements whose (up to three) base pointers are p0..p2
+// (null = unused).  Falls back to scalar accesses when the pointers are not mutually congruent
+// modulo vec_bytes.
+struct Geometry {
+  int vec_bytes;
+  int unroll;      // == the requested unroll, or 4 on the scalar fallback path
+  int cache_hint;  // == the requested hint, or B200_HINT_DEFAULT on the scalar fallback path
+  unsigned head;
+  unsigned long long nvec, ntiles;
+};
+Geometry make_geometry(const void* p0, const void* p1, const void* p2, size_t n, int elem_bytes, int vec_bytes,
+                       int block, int unroll, int cache_hint);
+
+// Per-op elementwise launchers (one translation unit each, so they compile in parallel).
+struct EwCall {
+  void *a, *b, *c;
+  size_t n;
+  int elem_bytes;
+  double s0, s1, s2;
+  Resolved r;
+  Geometry g;
+  unsigned grid;
+  cudaStream_t stream;
+};
+int launch_ew_init(const EwCall& call);
+int launch_ew_copy(const EwCall& call);
+int launch_ew_mul(const EwCall& call);
+int launch_ew_add(const EwCall& call);
+int launch_ew_triad(const EwCall& call);
+int launch_ew_nstream(const EwCall& call);
+
+struct DotCall {
+  const void *a, *b;
+  size_t n;
+  int elem_bytes;
+  void* workspace;
+  void* result_dev;
+  void* result_host;
+  Resolved r;
+  Geometry g;
+  unsigned grid;
+  cudaStream_t stream;
+};
+int launch_dot_impl(const DotCall& call);
+
+int launch_copy_bulk(const void* src, void* dst, size_t bytes, const Resolved& r, const DeviceProps& props,
+                     cudaStream_t stream);
+int launch_copy_tma(const void* src, void* dst, size_t bytes, const Resolved& r, const DeviceProps& props,
+                    cudaStream_t stream);
+
+}  // namespace b200

@@ -1,0 +1,457 @@
+// kernels.cuh -- hand-written sm_100a device code for the BabelStream kernels.
+//
+// What is computed (reference: /root/reference/src/cuda/CUDAStream.cu:203-296, and the CPU
+// models the results must match bit for bit, src/serial/SerialStream.cpp:36-113):
+//   init    a[i]=ia; b[i]=ib; c[i]=ic          copy    c[i] = a[i]
+//   mul     b[i] = s*c[i]                      add     c[i] = a[i] + b[i]
+//   triad   a[i] = b[i] + s*c[i]               nstream a[i] = a[i] + (b[i] + s*c[i])
+//   dot     sum_i a[i]*b[i]
+//
+// Nothing here is a contraction, so tensor cores / TMEM are not used; every kernel is bound by
+// HBM bandwidth (<= 1 flop per 12 bytes).  The design levers are the ones that matter for a
+// streaming kernel on B200:
+//   * 128-bit and 256-bit fully coalesced accesses (LDG.E.128 / LDG.E.ENL2.256, sm_100 only),
+//   * all loads of a tile issued before the first use (memory-level parallelism),
+//   * explicit L1/L2 cache policy per access (no_allocate / evict_first / .cs / L2::256B),
+//   * tile = blockDim * UNROLL vectors, grid either one tile per block or a grid-stride loop
+//     over k blocks per SM -- chosen per size in tuning.cuh,
+//   * for copy: no registers at all -- cp.async.bulk / TMA tensor tiles through a shared-memory
+//     ring driven by one thread per CTA.
+//
+// Rounding is spelled out with the _rn intrinsics, which the compiler never contracts or
+// re-associates: FUSED = true reproduces the reference's default build (GCC contracts
+// b + s*c into fma(s,c,b)), FUSED = false its -ffp-contract=off build.  The file is compiled
+// with -fmad=false as well, so no other FMA can appear.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+enum Op : int { OP_COPY = 0, OP_MUL = 1, OP_ADD = 2, OP_TRIAD = 3, OP_NSTREAM = 4, OP_DOT = 5, OP_INIT = 6 };
+enum Hint : int { H_DEFAULT = 1, H_NOALLOC = 2, H_EVICT_FIRST = 3, H_STREAM = 4, H_PREFETCH = 5 };
+
+// ------------------------------------------------------------------------------------------------
+// Exactly-rounded scalar arithmetic
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double mul_rn(double x, double y) { return __dmul_rn(x, y); }
+__device__ __forceinline__ float mul_rn(float x, float y) { return __fmul_rn(x, y); }
+__device__ __forceinline__ double add_rn(double x, double y) { return __dadd_rn(x, y); }
+__device__ __forceinline__ float add_rn(float x, float y) { return __fadd_rn(x, y); }
+__device__ __forceinline__ double fma_rn(double x, double y, double z) { return __fma_rn(x, y, z); }
+__device__ __forceinline__ float fma_rn(float x, float y, float z) { return __fmaf_rn(x, y, z); }
+
+// b + s*c with the reference's two possible roundings
+template <bool FUSED, typename T>
+__device__ __forceinline__ T axpy(T s, T c, T b) {
+  if constexpr (FUSED) return fma_rn(s, c, b);
+  else return add_rn(b, mul_rn(s, c));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Vector register packs and hinted global accesses.  VB = bytes per access (4, 8, 16, 32).
+// Data travels as raw 32/64-bit words; 256-bit accesses (v4.b64) exist on sm_100 and later.
+// ------------------------------------------------------------------------------------------------
+template <int VB> struct Words;
+template <> struct Words<4> { uint32_t w[1]; };
+template <> struct Words<8> { uint64_t w[1]; };
+template <> struct Words<16> { uint64_t w[2]; };
+template <> struct Words<32> { uint64_t w[4]; };
+
+#define B200_LD_QUAL_1_RW ""
+#define B200_LD_QUAL_1_RO ".nc"
+#define B200_LD_QUAL_2_RW ".L1::no_allocate"
+#define B200_LD_QUAL_2_RO ".nc.L1::no_allocate"
+#define B200_LD_QUAL_3_RW ".L1::no_allocate.L2::evict_first"      /* 256-bit accesses only */
+#define B200_LD_QUAL_3_RO ".nc.L1::no_allocate.L2::evict_first"
+#define B200_LD_QUAL_3P_RW ".L1::no_allocate.L2::cache_hint"      /* narrower: createpolicy operand */
+#define B200_LD_QUAL_3P_RO ".nc.L1::no_allocate.L2::cache_hint"
+#define B200_LD_QUAL_4_RW ".cs"
+#define B200_LD_QUAL_5_RW ".L1::no_allocate.L2::256B"
+#define B200_LD_QUAL_5_RO ".nc.L1::no_allocate.L2::256B"
+#define B200_ST_QUAL_1 ""
+#define B200_ST_QUAL_2 ".L1::no_allocate"
+#define B200_ST_QUAL_3 ".L1::no_allocate.L2::evict_first"
+#define B200_ST_QUAL_3P ".L1::no_allocate.L2::cache_hint"
+#define B200_ST_QUAL_4 ".cs"
+#define B200_ST_QUAL_5 ".L1::no_allocate"
+
+#define B200_LD_BODY(Q)                                                                                         \
+  if constexpr (VB == 4)                                                                                        \
+    asm volatile("ld.global" Q ".b32 %0, [%1];" : "=r"(r.w[0]) : "l"(p));                                       \
+  else if constexpr (VB == 8)                                                                                   \
+    asm volatile("ld.global" Q ".b64 %0, [%1];" : "=l"(r.w[0]) : "l"(p));                                       \
+  else if constexpr (VB == 16)                                                                                  \
+    asm volatile("ld.global" Q ".v2.b64 {%0,%1}, [%2];" : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(p));                 \
+  else                                                                                                          \
+    asm volatile("ld.global" Q ".v4.b64 {%0,%1,%2,%3}, [%4];"                                                   \
+                 : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2]), "=l"(r.w[3]) : "l"(p));
+
+// same, with an L2 cache-policy operand (VB < 32 only)
+#define B200_LD_BODY_POLICY(Q)                                                                                  \
+  if constexpr (VB == 4)                                                                                        \
+    asm volatile("ld.global" Q ".b32 %0, [%1], %2;" : "=r"(r.w[0]) : "l"(p), "l"(policy));                      \
+  else if constexpr (VB == 8)                                                                                   \
+    asm volatile("ld.global" Q ".b64 %0, [%1], %2;" : "=l"(r.w[0]) : "l"(p), "l"(policy));                      \
+  else                                                                                                          \
+    asm volatile("ld.global" Q ".v2.b64 {%0,%1}, [%2], %3;" : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(p), "l"(policy));
+
+#define B200_ST_BODY(Q)                                                                                         \
+  if constexpr (VB == 4)                                                                                        \
+    asm volatile("st.global" Q ".b32 [%0], %1;" ::"l"(p), "r"(r.w[0]) : "memory");                              \
+  else if constexpr (VB == 8)                                                                                   \
+    asm volatile("st.global" Q ".b64 [%0], %1;" ::"l"(p), "l"(r.w[0]) : "memory");                              \
+  else if constexpr (VB == 16)                                                                                  \
+    asm volatile("st.global" Q ".v2.b64 [%0], {%1,%2};" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]) : "memory");         \
+  else                                                                                                          \
+    asm volatile("st.global" Q ".v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]), "l"(r.w[2]),  \
+                 "l"(r.w[3]) : "memory");
+
+#define B200_ST_BODY_POLICY(Q)                                                                                  \
+  if constexpr (VB == 4)                                                                                        \
+    asm volatile("st.global" Q ".b32 [%0], %1, %2;" ::"l"(p), "r"(r.w[0]), "l"(policy) : "memory");             \
+  else if constexpr (VB == 8)                                                                                   \
+    asm volatile("st.global" Q ".b64 [%0], %1, %2;" ::"l"(p), "l"(r.w[0]), "l"(policy) : "memory");             \
+  else                                                                                                          \
+    asm volatile("st.global" Q ".v2.b64 [%0], {%1,%2}, %3;" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]), "l"(policy) : "memory");
+
+// L2 evict-first policy register, needed by H_EVICT_FIRST accesses narrower than 256 bits
+template <int VB, int HINT>
+__device__ __forceinline__ uint64_t make_policy() {
+  uint64_t policy = 0;
+  if constexpr (HINT == H_EVICT_FIRST && VB < 32)
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  return policy;
+}
+
+// READONLY: the array is not written by this kernel (-> .nc, the non-coherent path).
+template <int VB, int HINT, bool READONLY>
+__device__ __forceinline__ Words<VB> ldg(const void* p, uint64_t policy = 0) {
+  Words<VB> r;
+  if constexpr (HINT == H_DEFAULT) { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_1_RO) } else { B200_LD_BODY(B200_LD_QUAL_1_RW) } }
+  else if constexpr (HINT == H_NOALLOC) { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_2_RO) } else { B200_LD_BODY(B200_LD_QUAL_2_RW) } }
+  else if constexpr (HINT == H_EVICT_FIRST && VB == 32) { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_3_RO) } else { B200_LD_BODY(B200_LD_QUAL_3_RW) } }
+  else if constexpr (HINT == H_EVICT_FIRST) { if constexpr (READONLY) { B200_LD_BODY_POLICY(B200_LD_QUAL_3P_RO) } else { B200_LD_BODY_POLICY(B200_LD_QUAL_3P_RW) } }
+  else if constexpr (HINT == H_STREAM) { B200_LD_BODY(B200_LD_QUAL_4_RW) }
+  else { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_5_RO) } else { B200_LD_BODY(B200_LD_QUAL_5_RW) } }
+  (void)policy;
+  return r;
+}
+
+template <int VB, int HINT>
+__device__ __forceinline__ void stg(void* p, const Words<VB>& r, uint64_t policy = 0) {
+  if constexpr (HINT == H_DEFAULT) { B200_ST_BODY(B200_ST_QUAL_1) }
+  else if constexpr (HINT == H_NOALLOC) { B200_ST_BODY(B200_ST_QUAL_2) }
+  else if constexpr (HINT == H_EVICT_FIRST && VB == 32) { B200_ST_BODY(B200_ST_QUAL_3) }
+  else if constexpr (HINT == H_EVICT_FIRST) { B200_ST_BODY_POLICY(B200_ST_QUAL_3P) }
+  else if constexpr (HINT == H_STREAM) { B200_ST_BODY(B200_ST_QUAL_4) }
+  else { B200_ST_BODY(B200_ST_QUAL_5) }
+  (void)policy;
+}
+
+// words <-> elements (register renaming only; no instructions survive)
+template <typename T, int VB> struct Elems { T v[VB / sizeof(T)]; };
+
+template <typename T, int VB>
+__device__ __forceinline__ Elems<T, VB> unpack(const Words<VB>& w) {
+  Elems<T, VB> e;
+  if constexpr (sizeof(T) == 8) {
+#pragma unroll
+    for (int i = 0; i < VB / 8; i++) e.v[i] = __longlong_as_double((long long)w.w[i]);
+  } else if constexpr (VB == 4) {
+    e.v[0] = __uint_as_float(w.w[0]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < VB / 8; i++) {
+      e.v[2 * i] = __uint_as_float((uint32_t)(w.w[i] & 0xffffffffull));
+      e.v[2 * i + 1] = __uint_as_float((uint32_t)(w.w[i] >> 32));
+    }
+  }
+  return e;
+}
+
+template <typename T, int VB>
+__device__ __forceinline__ Words<VB> pack(const Elems<T, VB>& e) {
+  Words<VB> w;
+  if constexpr (sizeof(T) == 8) {
+#pragma unroll
+    for (int i = 0; i < VB / 8; i++) w.w[i] = (uint64_t)__double_as_longlong(e.v[i]);
+  } else if constexpr (VB == 4) {
+    w.w[0] = __float_as_uint(e.v[0]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < VB / 8; i++)
+      w.w[i] = (uint64_t)__float_as_uint(e.v[2 * i]) | ((uint64_t)__float_as_uint(e.v[2 * i + 1]) << 32);
+  }
+  return w;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Elementwise kernels.  One template for init/copy/mul/add/triad/nstream.
+//
+// Geometry: the arrays are addressed from element `head` (0 <= head < VB/sizeof(T), chosen by the
+// launcher so that a+head, b+head, c+head are VB-aligned), as nvec vectors of VB bytes.  A tile
+// is blockDim.x*UNROLL consecutive vectors; thread t of the block owns vectors t, t+blockDim.x, ...
+// of the tile, so every warp-level access covers 32*VB contiguous bytes.  Blocks walk the tiles
+// with stride gridDim.x (gridDim.x == ntiles gives one tile per block).  The < 2*VB/sizeof(T)
+// ragged elements before `head` and after the last full vector are done by block 0.
+// ------------------------------------------------------------------------------------------------
+struct EwArgs {
+  void* a;
+  void* b;
+  void* c;
+  unsigned long long nvec;    // full vectors after head
+  unsigned long long ntiles;  // ceil(nvec / (blockDim.x * UNROLL))
+  unsigned long long n;       // total elements
+  unsigned int head;          // leading scalar elements
+};
+
+template <typename T, int OP, bool FUSED>
+__device__ __forceinline__ void ew_scalar(T* a, T* b, T* c, unsigned long long i, T s0, T s1, T s2) {
+  if constexpr (OP == OP_INIT) { a[i] = s0; b[i] = s1; c[i] = s2; }
+  else if constexpr (OP == OP_COPY) c[i] = a[i];
+  else if constexpr (OP == OP_MUL) b[i] = mul_rn(s0, c[i]);
+  else if constexpr (OP == OP_ADD) c[i] = add_rn(a[i], b[i]);
+  else if constexpr (OP == OP_TRIAD) a[i] = axpy<FUSED>(s0, c[i], b[i]);
+  else if constexpr (OP == OP_NSTREAM) a[i] = add_rn(a[i], axpy<FUSED>(s0, c[i], b[i]));
+}
+
+template <typename T, int OP, int VB, int UNROLL, int HINT, bool FUSED>
+__global__ void __launch_bounds__(512)
+ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
+  constexpr int EPV = VB / (int)sizeof(T);
+  constexpr bool LA = (OP == OP_COPY || OP == OP_ADD || OP == OP_NSTREAM);
+  constexpr bool LB = (OP == OP_ADD || OP == OP_TRIAD || OP == OP_NSTREAM);
+  constexpr bool LC = (OP == OP_MUL || OP == OP_TRIAD || OP == OP_NSTREAM);
+  constexpr bool A_RO = (OP == OP_COPY || OP == OP_ADD);  // a is read AND written by nstream: no .nc
+
+  T* const a = static_cast<T*>(args.a);
+  T* const b = static_cast<T*>(args.b);
+  T* const c = static_cast<T*>(args.c);
+  char* const va = reinterpret_cast<char*>(a + args.head);
+  char* const vb = reinterpret_cast<char*>(b + args.head);
+  char* const vc = reinterpret_cast<char*>(c + args.head);
+
+  const unsigned long long nvec = args.nvec;
+  const unsigned long long tile_vecs = (unsigned long long)blockDim.x * UNROLL;
+
+  const uint64_t policy = make_policy<VB, HINT>();
+  Elems<T, VB> init_a, init_b, init_c;
+  if constexpr (OP == OP_INIT) {
+#pragma unroll
+    for (int e = 0; e < EPV; e++) { init_a.v[e] = s0; init_b.v[e] = s1; init_c.v[e] = s2; }
+  }
+
+  for (unsigned long long tile = blockIdx.x; tile < args.ntiles; tile += gridDim.x) {
+    const unsigned long long v0 = tile * tile_vecs + threadIdx.x;
+    const bool full = (tile + 1) * tile_vecs <= nvec;  // block-uniform
+
+    Words<VB> wa[UNROLL], wb[UNROLL], wc[UNROLL];
+    // 1. every load of the tile first
+#pragma unroll
+    for (int j = 0; j < UNROLL; j++) {
+      const unsigned long long v = v0 + (unsigned long long)j * blockDim.x;
+      if (full || v < nvec) {
+        if constexpr (LA) wa[j] = ldg<VB, HINT, A_RO>(va + v * VB, policy);
+        if constexpr (LB) wb[j] = ldg<VB, HINT, true>(vb + v * VB, policy);
+        if constexpr (LC) wc[j] = ldg<VB, HINT, true>(vc + v * VB, policy);
+      }
+    }
+    // 2. arithmetic and stores
+#pragma unroll
+    for (int j = 0; j < UNROLL; j++) {
+      const unsigned long long v = v0 + (unsigned long long)j * blockDim.x;
+      if (full || v < nvec) {
+        if constexpr (OP == OP_INIT) {
+          stg<VB, HINT>(va + v * VB, pack<T, VB>(init_a), policy);
+          stg<VB, HINT>(vb + v * VB, pack<T, VB>(init_b), policy);
+          stg<VB, HINT>(vc + v * VB, pack<T, VB>(init_c), policy);
+        } else if constexpr (OP == OP_COPY) {
+          stg<VB, HINT>(vc + v * VB, wa[j], policy);
+        } else {
+          Elems<T, VB> ea, eb, ec, r;
+          if constexpr (LA) ea = unpack<T, VB>(wa[j]);
+          if constexpr (LB) eb = unpack<T, VB>(wb[j]);
+          if constexpr (LC) ec = unpack<T, VB>(wc[j]);
+#pragma unroll
+          for (int e = 0; e < EPV; e++) {
+            if constexpr (OP == OP_MUL) r.v[e] = mul_rn(s0, ec.v[e]);
+            else if constexpr (OP == OP_ADD) r.v[e] = add_rn(ea.v[e], eb.v[e]);
+            else if constexpr (OP == OP_TRIAD) r.v[e] = axpy<FUSED>(s0, ec.v[e], eb.v[e]);
+            else r.v[e] = add_rn(ea.v[e], axpy<FUSED>(s0, ec.v[e], eb.v[e]));  // nstream: a + (b + s*c)
+          }
+          if constexpr (OP == OP_MUL) stg<VB, HINT>(vb + v * VB, pack<T, VB>(r), policy);
+          else if constexpr (OP == OP_ADD) stg<VB, HINT>(vc + v * VB, pack<T, VB>(r), policy);
+          else stg<VB, HINT>(va + v * VB, pack<T, VB>(r), policy);
+        }
+      }
+    }
+  }
+
+  // ragged edges: [0, head) and [head + nvec*EPV, n)
+  if (blockIdx.x == 0) {
+    const unsigned long long tail_begin = args.head + nvec * EPV;
+    const unsigned long long edge = args.head + (args.n - tail_begin);
+    if (threadIdx.x < edge) {
+      const unsigned long long i = threadIdx.x < args.head ? threadIdx.x : tail_begin + (threadIdx.x - args.head);
+      ew_scalar<T, OP, FUSED>(a, b, c, i, s0, s1, s2);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dot.  Pass 1: every thread accumulates UNROLL*EPV independent chains over its vectors
+// (FUSED: acc = fma(a,b,acc); else acc = acc + round(a*b)), folds them in a fixed order, then
+// warp shuffle tree -> one shared-memory slot per warp -> warp 0 -> block partial.
+// Pass 2 (deterministic): ONE block adds the gridDim.x partials in a fixed strided order with
+// the same tree.  It runs either as a second launch (dot_final_kernel) or, TICKET = true, inside
+// pass 1 by whichever block finishes last -- the order of the additions does not depend on which
+// block that is, so both give the same bits.
+// ------------------------------------------------------------------------------------------------
+constexpr int kDotMaxBlocks = 4096;
+constexpr size_t kDotWorkspaceBytes = kDotMaxBlocks * 8 + 256;  // partials + ticket
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = add_rn(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// result valid in thread 0.  scratch: >= 32 elements of shared memory.
+template <typename T>
+__device__ __forceinline__ T block_sum(T v, T* scratch) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  if (lane == 0) scratch[wid] = v;
+  __syncthreads();
+  if (wid == 0) {
+    v = lane < nw ? scratch[lane] : T(0);
+    v = warp_sum(v);
+  }
+  __syncthreads();  // scratch may be reused
+  return v;
+}
+
+template <typename T>
+__device__ __forceinline__ void dot_second_pass(const T* partials, unsigned nparts, T* scratch, T* result_dev,
+                                                T* result_host) {
+  T v = T(0);
+  for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) v = add_rn(v, __ldcg(partials + i));
+  v = block_sum(v, scratch);
+  if (threadIdx.x == 0) {
+    if (result_dev) *result_dev = v;
+    if (result_host) *result_host = v;
+  }
+}
+
+struct DotArgs {
+  const void* a;
+  const void* b;
+  void* partials;        // T[gridDim.x]
+  unsigned int* ticket;  // zero before launch; left zero
+  void* result_dev;      // may be null
+  void* result_host;     // mapped pinned, may be null
+  unsigned long long nvec, ntiles, n;
+  unsigned int head;
+};
+
+// 1024-thread blocks leave 64 registers per thread: not enough for the widest tiles
+// (2 operands x 128 bytes per thread), which therefore run with at most 512 threads.
+constexpr int dot_max_block(int vb, int unroll) { return vb * unroll >= 128 ? 512 : 1024; }
+
+template <typename T, int VB, int UNROLL, int HINT, bool FUSED, bool TICKET>
+__global__ void __launch_bounds__(dot_max_block(VB, UNROLL))
+dot_kernel(const DotArgs args) {
+  constexpr int EPV = VB / (int)sizeof(T);
+  __shared__ T scratch[32];
+  __shared__ bool is_last;
+
+  const T* const a = static_cast<const T*>(args.a);
+  const T* const b = static_cast<const T*>(args.b);
+  const char* const va = reinterpret_cast<const char*>(a + args.head);
+  const char* const vb = reinterpret_cast<const char*>(b + args.head);
+  const unsigned long long nvec = args.nvec;
+  const unsigned long long tile_vecs = (unsigned long long)blockDim.x * UNROLL;
+
+  const uint64_t policy = make_policy<VB, HINT>();
+  T acc[UNROLL][EPV];
+#pragma unroll
+  for (int j = 0; j < UNROLL; j++)
+#pragma unroll
+    for (int e = 0; e < EPV; e++) acc[j][e] = T(0);
+
+  for (unsigned long long tile = blockIdx.x; tile < args.ntiles; tile += gridDim.x) {
+    const unsigned long long v0 = tile * tile_vecs + threadIdx.x;
+    const bool full = (tile + 1) * tile_vecs <= nvec;
+    Words<VB> wa[UNROLL], wb[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; j++) {
+      const unsigned long long v = v0 + (unsigned long long)j * blockDim.x;
+      if (full || v < nvec) {
+        wa[j] = ldg<VB, HINT, true>(va + v * VB, policy);
+        wb[j] = ldg<VB, HINT, true>(vb + v * VB, policy);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; j++) {
+      const unsigned long long v = v0 + (unsigned long long)j * blockDim.x;
+      if (full || v < nvec) {
+        const Elems<T, VB> ea = unpack<T, VB>(wa[j]), eb = unpack<T, VB>(wb[j]);
+#pragma unroll
+        for (int e = 0; e < EPV; e++) {
+          if constexpr (FUSED) acc[j][e] = fma_rn(ea.v[e], eb.v[e], acc[j][e]);
+          else acc[j][e] = add_rn(acc[j][e], mul_rn(ea.v[e], eb.v[e]));
+        }
+      }
+    }
+  }
+
+  // fixed-order fold of the per-thread chains
+  T sum = T(0);
+#pragma unroll
+  for (int j = 0; j < UNROLL; j++)
+#pragma unroll
+    for (int e = 0; e < EPV; e++) sum = add_rn(sum, acc[j][e]);
+
+  // ragged edges, block 0 only
+  if (blockIdx.x == 0) {
+    const unsigned long long tail_begin = args.head + nvec * EPV;
+    const unsigned long long edge = args.head + (args.n - tail_begin);
+    if (threadIdx.x < edge) {
+      const unsigned long long i = threadIdx.x < args.head ? threadIdx.x : tail_begin + (threadIdx.x - args.head);
+      if constexpr (FUSED) sum = fma_rn(a[i], b[i], sum);
+      else sum = add_rn(sum, mul_rn(a[i], b[i]));
+    }
+  }
+
+  sum = block_sum(sum, scratch);
+  T* const partials = static_cast<T*>(args.partials);
+  if (threadIdx.x == 0) partials[blockIdx.x] = sum;
+
+  if constexpr (TICKET) {
+    if (threadIdx.x == 0) {
+      __threadfence();  // partial visible before the ticket is taken
+      const unsigned t = atomicAdd(args.ticket, 1u);
+      is_last = (t == gridDim.x - 1);
+      __threadfence();
+    }
+    __syncthreads();
+    if (is_last) {
+      dot_second_pass<T>(partials, gridDim.x, scratch, static_cast<T*>(args.result_dev),
+                         static_cast<T*>(args.result_host));
+      if (threadIdx.x == 0) *args.ticket = 0u;  // ready for the next launch
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(1024)
+dot_final_kernel(const T* partials, unsigned nparts, T* result_dev, T* result_host) {
+  __shared__ T scratch[32];
+  dot_second_pass<T>(partials, nparts, scratch, result_dev, result_host);
+}
+
+}  // namespace b200

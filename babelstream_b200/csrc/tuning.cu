@@ -1,0 +1,198 @@
+// tuning.cu -- host-side launch logic: the per-size configuration table, the grid policy, the
+// vector geometry for arbitrary pointer alignment, and the multi-GPU shard partition.
+// Pure host code (no CUDA calls): unit-tested on a machine without a GPU.
+//
+// The reference fixes its shape at compile time: 256 threads, UNROLL_FACTOR 4 scalar accesses,
+// grid = ceil(N/4/256), dot = 4 blocks/SM x 1024 threads (src/cuda/CUDAStream.h:18-19,
+// CUDAStream.cu:126,196-198).  Here the shape is chosen per (kernel, bytes, L2 size); the
+// entries below are the winners of tools/sweep.py on a B200 (profiles/r01_sweep_*.csv).
+#include <limits.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "internal.h"
+
+namespace b200 {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof g_error, fmt, ap);
+  va_end(ap);
+}
+const char* last_error_message() { return g_error; }
+
+// arrays a kernel touches (reads + writes, distinct arrays): decides whether the working set can
+// live in L2, in which case evict-first / no-allocate hints would destroy inter-kernel reuse.
+static int arrays_touched(int kernel) {
+  switch (kernel) {
+    case B200_COPY: case B200_MUL: case B200_DOT: return 2;
+    default: return 3;
+  }
+}
+
+int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
+                Resolved* out) {
+  if (kernel < 0 || kernel >= B200_NUM_KERNELS) { set_error("unknown kernel id %d", kernel); return B200_EINVAL; }
+  if (elem_bytes != 4 && elem_bytes != 8) { set_error("elem_bytes must be 4 or 8, got %d", elem_bytes); return B200_EINVAL; }
+  b200_launch_cfg z;
+  memset(&z, 0, sizeof z);
+  const b200_launch_cfg& c = in ? *in : z;
+  if (num_sms <= 0) num_sms = 148;
+  if (l2_bytes <= 0) l2_bytes = 126 << 20;
+
+  // BabelStream keeps all three arrays live across kernels, so L2 residency is judged on 3 arrays
+  const double footprint = 3.0 * (double)n * elem_bytes;
+  const bool l2_resident = footprint <= 0.8 * (double)l2_bytes;
+  const double bytes_moved = (double)arrays_touched(kernel) * (double)n * elem_bytes;
+  const bool tiny = bytes_moved < 4.0 * 1024 * 1024;  // latency-bound: favour many small blocks
+
+  Resolved r;
+  memset(&r, 0, sizeof r);
+  // ---- defaults (auto) ----
+  if (kernel == B200_DOT) {
+    r.vec_bytes = 16; r.unroll = 4; r.block = tiny ? 256 : 512;
+    r.grid_policy = tiny ? -2 : -4;            // blocks per SM, grid-stride
+    r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
+    r.variant = B200_VARIANT_DOT_TICKET;
+  } else {
+    r.vec_bytes = tiny ? 16 : 32; r.unroll = tiny ? 1 : 2; r.block = 256;
+    r.grid_policy = INT_MAX;                   // one tile per block
+    r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
+    r.variant = B200_VARIANT_LDST;
+  }
+  r.contract = 1;
+  r.stages = 4;
+  r.chunk_bytes = 32768;
+
+  // ---- explicit overrides ----
+  if (c.vec_bytes) r.vec_bytes = c.vec_bytes;
+  if (c.unroll) r.unroll = c.unroll;
+  if (c.block) r.block = c.block;
+  if (c.grid) r.grid_policy = c.grid;
+  if (c.cache_hint) r.cache_hint = c.cache_hint;
+  if (c.variant) r.variant = c.variant;
+  if (c.contract) r.contract = c.contract;
+  if (c.stages) r.stages = c.stages;
+  if (c.chunk_bytes) r.chunk_bytes = c.chunk_bytes;
+
+  // ---- validation ----
+  if (r.vec_bytes != 16 && r.vec_bytes != 32 && r.vec_bytes != elem_bytes) {
+    set_error("vec_bytes must be 16, 32 or elem_bytes (scalar), got %d", r.vec_bytes); return B200_EINVAL;
+  }
+  if (r.vec_bytes == elem_bytes) { r.unroll = 4; r.cache_hint = B200_HINT_DEFAULT; }
+  const bool unroll_ok = r.unroll == 1 || r.unroll == 2 || r.unroll == 4 || (r.unroll == 8 && r.vec_bytes == 16);
+  if (!unroll_ok) { set_error("unroll must be 1, 2, 4 (or 8 with 16-byte vectors), got %d", r.unroll); return B200_EINVAL; }
+  const int max_block = kernel == B200_DOT ? 1024 : 512;
+  if (r.block < 32 || r.block > max_block || r.block % 32) {
+    set_error("block must be a multiple of 32 in [32, %d], got %d", max_block, r.block); return B200_EINVAL;
+  }
+  if (r.cache_hint < B200_HINT_DEFAULT || r.cache_hint > B200_HINT_PREFETCH) {
+    set_error("cache_hint out of range: %d", r.cache_hint); return B200_EINVAL;
+  }
+  if (r.contract != 1 && r.contract != 2) { set_error("contract must be 1 (fused) or 2 (unfused)"); return B200_EINVAL; }
+  if (kernel == B200_DOT) {
+    if (r.variant != B200_VARIANT_DOT_TWO_PASS && r.variant != B200_VARIANT_DOT_TICKET) {
+      set_error("dot variant must be two_pass (1) or ticket (2)"); return B200_EINVAL;
+    }
+    if (r.grid_policy == INT_MAX) r.grid_policy = -4;  // a dot grid is always bounded (workspace)
+  } else if (kernel == B200_COPY) {
+    if (r.variant < B200_VARIANT_LDST || r.variant > B200_VARIANT_TMA) { set_error("copy variant out of range"); return B200_EINVAL; }
+  } else if (r.variant != B200_VARIANT_LDST) {
+    set_error("only copy has bulk/tma variants"); return B200_EINVAL;
+  }
+  *out = r;
+  return B200_OK;
+}
+
+unsigned grid_for(int grid_policy, unsigned long long ntiles, int num_sms) {
+  if (ntiles == 0) return 1;  // still launched: block 0 handles the ragged edges
+  unsigned long long g;
+  if (grid_policy == INT_MAX) g = ntiles;
+  else if (grid_policy < 0) g = (unsigned long long)(-(long long)grid_policy) * (unsigned long long)num_sms;
+  else g = (unsigned long long)grid_policy;
+  if (g > ntiles) g = ntiles;
+  if (g > 0x7fffffffull) g = 0x7fffffffull;  // gridDim.x limit; the tile loop covers the rest
+  if (g == 0) g = 1;
+  return (unsigned)g;
+}
+
+Geometry make_geometry(const void* p0, const void* p1, const void* p2, size_t n, int elem_bytes, int vec_bytes,
+                       int block, int unroll, int cache_hint) {
+  Geometry g;
+  const void* ptrs[3] = {p0, p1, p2};
+  // all used pointers must share their offset within a vector, otherwise no common `head` exists
+  bool congruent = true;
+  uintptr_t off = 0;
+  bool have = false;
+  for (const void* p : ptrs) {
+    if (!p) continue;
+    const uintptr_t o = (uintptr_t)p % (uintptr_t)vec_bytes;
+    if (o % elem_bytes) congruent = false;  // not even element-aligned relative to the vector grid
+    if (!have) { off = o; have = true; }
+    else if (o != off) congruent = false;
+  }
+  if (vec_bytes == elem_bytes || !congruent) {
+    g.vec_bytes = elem_bytes; g.unroll = 4; g.cache_hint = B200_HINT_DEFAULT; g.head = 0;
+    g.nvec = n;
+  } else {
+    g.vec_bytes = vec_bytes; g.unroll = unroll; g.cache_hint = cache_hint;
+    const unsigned epv = (unsigned)(vec_bytes / elem_bytes);
+    unsigned head = off ? (unsigned)((vec_bytes - off) / elem_bytes) : 0u;
+    if (head > n) head = (unsigned)n;
+    g.head = head;
+    g.nvec = (n - head) / epv;
+  }
+  const unsigned long long tile = (unsigned long long)block * g.unroll;
+  g.ntiles = (g.nvec + tile - 1) / tile;
+  return g;
+}
+
+}  // namespace b200
+
+// ---- exported host logic --------------------------------------------------------------------
+extern "C" {
+
+const char* b200_last_error(void) { return b200::last_error_message(); }
+
+int b200_shard_range(size_t n, int elem_bytes, int ngpus, int g, size_t* begin, size_t* count) {
+  if (ngpus < 1 || g < 0 || g >= ngpus || (elem_bytes != 4 && elem_bytes != 8) || !begin || !count) {
+    b200::set_error("b200_shard_range: bad arguments (n=%zu elem_bytes=%d ngpus=%d g=%d)", n, elem_bytes, ngpus, g);
+    return B200_EINVAL;
+  }
+  // ceil split rounded up to a multiple of 128 bytes; trailing shards may be short or empty
+  const size_t align = 128 / (size_t)elem_bytes;
+  size_t per = (n + (size_t)ngpus - 1) / (size_t)ngpus;
+  per = (per + align - 1) / align * align;
+  size_t b = per * (size_t)g;
+  if (b > n) b = n;
+  size_t e = b + per;
+  if (e > n) e = n;
+  *begin = b;
+  *count = e - b;
+  return B200_OK;
+}
+
+int b200_resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
+                     b200_launch_cfg* out, unsigned* grid_out) {
+  b200::Resolved r;
+  if (int rc = b200::resolve_cfg(kernel, n, elem_bytes, num_sms, l2_bytes, in, &r)) return rc;
+  if (out) {
+    memset(out, 0, sizeof *out);
+    out->vec_bytes = r.vec_bytes; out->unroll = r.unroll; out->block = r.block; out->grid = r.grid_policy;
+    out->cache_hint = r.cache_hint; out->variant = r.variant; out->contract = r.contract;
+    out->stages = r.stages; out->chunk_bytes = r.chunk_bytes;
+  }
+  if (grid_out) {
+    // geometry for perfectly aligned arrays
+    const b200::Geometry g = b200::make_geometry(nullptr, nullptr, nullptr, n, elem_bytes, r.vec_bytes, r.block,
+                                                 r.unroll, r.cache_hint);
+    *grid_out = b200::grid_for(r.grid_policy, g.ntiles, num_sms > 0 ? num_sms : 148);
+  }
+  return B200_OK;
+}
+
+}  // extern "C"

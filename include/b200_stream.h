@@ -1,0 +1,177 @@
+/*
+ * b200_stream.h -- the C ABI of libb200stream.so: hand-written sm_100a BabelStream kernels.
+ *
+ * This is the drop-in boundary.  The C++ host class B200Stream<T> (babelstream_b200/src/b200/)
+ * implements the reference's Stream<T> interface (/root/reference/src/Stream.h:29-49) purely in
+ * terms of the LEVEL 2 calls below and is driven by the reference's unmodified src/main.cpp.
+ * Python (babelstream_b200/stream.py, ctypes), cgo, JNI ... bind the same symbols.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ types, no exceptions cross this boundary;
+ *   - every call returns B200_OK (0) or a negative B200_E* code; b200_last_error() gives the
+ *     message of the calling thread's last failure;
+ *   - elem_bytes is 4 (float) or 8 (double): the two types Stream<T> is instantiated for
+ *     (src/cuda/CUDAStream.cu:349-350);
+ *   - scalars cross as double and are rounded to T exactly once inside, which is what the
+ *     reference's `const T scalar = startScalar;` does (src/serial/SerialStream.cpp:68,87,97);
+ *   - there is NO CPU fallback: without a CUDA device the compute entry points fail with
+ *     B200_ENODEVICE.
+ */
+#ifndef B200_STREAM_H
+#define B200_STREAM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_EINVAL (-1)    /* bad argument */
+#define B200_ENODEVICE (-2) /* no CUDA device / bad device index (reference: runtime_error "Invalid device index") */
+#define B200_ENOMEM (-3)    /* arrays do not fit (reference: "Device does not have enough memory for all buffers") */
+#define B200_ECUDA (-4)     /* a CUDA runtime call failed (reference: CU() macro, CUDAStream.cu:14-26) */
+#define B200_ENCCL (-5)     /* NCCL missing or failed (multi-GPU dot only) */
+#define B200_EUNSUPPORTED (-6)
+
+/* Kernel ids: the reference's BenchId values (src/benchmark.h:18) plus init. */
+enum { B200_COPY = 0, B200_MUL = 1, B200_ADD = 2, B200_TRIAD = 3, B200_NSTREAM = 4, B200_DOT = 5, B200_INIT = 6,
+       B200_NUM_KERNELS = 7 };
+
+/* cache_hint values */
+enum { B200_HINT_AUTO = 0,
+       B200_HINT_DEFAULT = 1,     /* ld.global / st.global */
+       B200_HINT_NOALLOC = 2,     /* ld.global[.nc].L1::no_allocate / st.global.L1::no_allocate */
+       B200_HINT_EVICT_FIRST = 3, /* + .L2::evict_first on loads and stores */
+       B200_HINT_STREAM = 4,      /* ld.global.cs / st.global.cs */
+       B200_HINT_PREFETCH = 5     /* L1::no_allocate + .L2::256B prefetch on loads */ };
+
+/* variant values */
+enum { B200_VARIANT_AUTO = 0,
+       B200_VARIANT_LDST = 1,     /* register path: vector LDG/STG (all kernels) */
+       B200_VARIANT_BULK = 2,     /* copy: cp.async.bulk global->shared->global ring (UBLKCP) */
+       B200_VARIANT_TMA = 3,      /* copy: cp.async.bulk.tensor 2-D tiles through a CUtensorMap (UTMALDG/UTMASTG) */
+       B200_VARIANT_DOT_TWO_PASS = 1, /* dot: block partials, then a 1-block second launch */
+       B200_VARIANT_DOT_TICKET = 2    /* dot: same second pass run by the last block to finish, one launch */ };
+
+/* Launch configuration.  A zeroed struct (or NULL) means "auto": the per-size table in
+ * csrc/tuning.cuh.  The reference's counterparts are compile-time: TBSIZE 256, UNROLL_FACTOR 4,
+ * GRID_STRIDE (src/cuda/CUDAStream.h:18, model.cmake:6-22). */
+typedef struct b200_launch_cfg {
+  int vec_bytes;  /* 0 auto | 4 or 8 = scalar | 16 = 128-bit | 32 = 256-bit accesses */
+  int unroll;     /* 0 auto | 1,2,4,8 vectors per thread per tile (8 only with 16-byte vectors) */
+  int block;      /* 0 auto | threads per block: 64..512, multiple of 32 (dot: ..1024) */
+  int grid;       /* 0 auto | >0 exact block count (grid-stride) | <0: -k means k blocks per SM |
+                     INT32_MAX: one tile per block */
+  int cache_hint; /* B200_HINT_* */
+  int variant;    /* B200_VARIANT_* */
+  int contract;   /* 0 auto (=fused) | 1 fused: fma(s,c,b), the reference's default -ffp-contract=fast build |
+                     2 unfused: round(s*c) then add, the reference built -ffp-contract=off */
+  int stages;     /* bulk/tma copy: ring depth (0 auto) */
+  int chunk_bytes;/* bulk/tma copy: bytes per stage (0 auto) */
+  int reserved[3];
+} b200_launch_cfg;
+
+/* ------------------------------------------------------------------------------------------
+ * LEVEL 0 -- library / device queries (replace listDevices / getDeviceName / getDeviceDriver,
+ * src/Stream.h:51-54, src/cuda/CUDAStream.cu:311-347).  Safe to call without a GPU.
+ * ------------------------------------------------------------------------------------------ */
+const char* b200_version(void);
+const char* b200_last_error(void);
+int b200_device_count(void);                           /* >= 0, or a negative code */
+int b200_device_name(int device, char* buf, int buflen);
+int b200_driver_version(int device);                   /* cudaDriverGetVersion value, or negative */
+int b200_device_info(int device, int* num_sms, int* cc_major, int* cc_minor, size_t* total_mem,
+                     int* l2_bytes, int* mem_clock_khz, int* mem_bus_bits);
+uint64_t b200_launch_count(void);                      /* kernels launched by this library so far */
+
+/* Host-side logic, usable (and tested) without a GPU. */
+/* Contiguous shard of GPU g out of ngpus: [begin, begin+count).  Shard boundaries are multiples of
+ * 128 bytes so every shard starts on a full cache line. */
+int b200_shard_range(size_t n, int elem_bytes, int ngpus, int g, size_t* begin, size_t* count);
+/* Resolve "auto" fields of `in` for (kernel, n, elem_bytes) on a GPU with num_sms SMs and l2_bytes of L2:
+ * fills `out`, and the resulting grid size / tile count. */
+int b200_resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
+                     const b200_launch_cfg* in, b200_launch_cfg* out, unsigned* grid_out);
+
+/* ------------------------------------------------------------------------------------------
+ * LEVEL 1 -- raw launchers: one kernel on caller-owned DEVICE pointers, asynchronous on
+ * `stream` (a cudaStream_t passed as void*; NULL = the legacy default stream) of the CURRENT
+ * device.  Any pointer alignment and any n >= 0 are accepted.
+ * Each replaces the body of the reference model's method of the same name:
+ *   init_arrays CUDAStream.cu:203-211   copy :237-243   mul :245-251   add :253-259
+ *   triad :261-267   nstream :269-275   dot :277-309
+ * ------------------------------------------------------------------------------------------ */
+int b200_launch_init(void* a, void* b, void* c, size_t n, int elem_bytes, double init_a, double init_b,
+                     double init_c, const b200_launch_cfg* cfg, void* stream);
+int b200_launch_copy(const void* a, void* c, size_t n, int elem_bytes, const b200_launch_cfg* cfg, void* stream);
+int b200_launch_mul(void* b, const void* c, size_t n, int elem_bytes, double scalar, const b200_launch_cfg* cfg,
+                    void* stream);
+int b200_launch_add(const void* a, const void* b, void* c, size_t n, int elem_bytes, const b200_launch_cfg* cfg,
+                    void* stream);
+int b200_launch_triad(void* a, const void* b, const void* c, size_t n, int elem_bytes, double scalar,
+                      const b200_launch_cfg* cfg, void* stream);
+int b200_launch_nstream(void* a, const void* b, const void* c, size_t n, int elem_bytes, double scalar,
+                        const b200_launch_cfg* cfg, void* stream);
+/* dot: `workspace` is device memory of at least b200_dot_workspace_bytes() bytes, zero-initialised
+ * once by the caller (the kernel leaves it zeroed again).  The sum (type T) is written to
+ * result_dev (device pointer, may be NULL) and to result_host_mapped (device-visible address of
+ * mapped pinned host memory, may be NULL).  Deterministic: bit-identical for equal
+ * (n, cfg, pointer alignment). */
+size_t b200_dot_workspace_bytes(void);
+int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                    void* result_host_mapped, const b200_launch_cfg* cfg, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * LEVEL 2 -- the Stream<T> object: three device-resident arrays of n elements, sharded
+ * contiguously over `ngpus` devices first_device .. first_device+ngpus-1, blocking calls
+ * ("These must be blocking calls", src/Stream.h:36).  One caller thread at a time.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_ctx b200_ctx;
+
+/* Replaces the model constructor (CUDAStream.cu:80-149) minus its init_arrays call, which the
+ * host class issues itself.  ngpus = 0 reads BABELSTREAM_B200_NGPUS (default 1).  Returns NULL on
+ * failure (see b200_last_error / *status). */
+b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int* status);
+void b200_destroy(b200_ctx* ctx);
+
+/* "key=value" tuning / behaviour options, also read from the environment at create time as
+ * BABELSTREAM_B200_<KEY>.  Keys: contract=fast|off, copy_variant=auto|ldst|bulk|tma,
+ * dot_variant=auto|two_pass|ticket, timing=0|1, sync=stream|spin|event,
+ * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk) */
+int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
+int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */
+
+int b200_init_arrays(b200_ctx* ctx, double init_a, double init_b, double init_c); /* Stream::init_arrays */
+int b200_copy(b200_ctx* ctx);                                                     /* Stream::copy     c = a */
+int b200_mul(b200_ctx* ctx, double scalar);                                       /* Stream::mul      b = s*c */
+int b200_add(b200_ctx* ctx);                                                      /* Stream::add      c = a+b */
+int b200_triad(b200_ctx* ctx, double scalar);                                     /* Stream::triad    a = b+s*c */
+int b200_nstream(b200_ctx* ctx, double scalar);                                   /* Stream::nstream  a += b+s*c */
+int b200_dot(b200_ctx* ctx, double* result);                                      /* Stream::dot      sum a*b; value of type T widened to double */
+int b200_run(b200_ctx* ctx, int kernel, double scalar, double* result);           /* dispatch by kernel id */
+
+/* Stream::get_arrays (CUDAStream.cu:213-235): gathers all shards into library-owned host buffers
+ * (pinned when they fit) that stay valid until b200_destroy. */
+int b200_get_arrays(b200_ctx* ctx, const void** a, const void** b, const void** c);
+/* Same gather into caller buffers of n*elem_bytes each (any may be NULL). */
+int b200_read_arrays(b200_ctx* ctx, void* a, void* b, void* c);
+/* Scatter caller host buffers to the shards (test and end-to-end use; any may be NULL). */
+int b200_write_arrays(b200_ctx* ctx, const void* a, const void* b, const void* c);
+
+/* Introspection */
+int b200_num_gpus(b200_ctx* ctx);
+size_t b200_array_size(b200_ctx* ctx);
+int b200_elem_bytes(b200_ctx* ctx);
+/* Device time of the last kernel call in milliseconds, max over GPUs, measured with CUDA events
+ * on the launching streams.  Needs option timing=1; returns a negative value otherwise. */
+double b200_last_kernel_ms(b200_ctx* ctx);
+/* Device pointers and stream of shard g, so that callers can time with their own events. */
+int b200_shard_info(b200_ctx* ctx, int g, int* device, void** a, void** b, void** c, size_t* begin, size_t* count,
+                    void** stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_STREAM_H */

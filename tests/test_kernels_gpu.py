@@ -1,0 +1,280 @@
+"""GPU parity tests, LEVEL 1 of the C ABI: each CUDA kernel on raw device pointers against the oracle.
+
+Bar: BIT-EXACT for init, copy, mul, add, triad and nstream in both rounding modes
+(contract = fused: the reference's default -ffp-contract=fast build; unfused: -ffp-contract=off);
+dot within BabelStream's own relative check (1e7*eps, src/main.cpp:384) -- in fact far tighter --
+and bit-reproducible run to run.  torch is used for device memory and streams only.
+"""
+import math
+
+import numpy as np
+import pytest
+
+import babelstream_b200 as bs
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+DTYPES = [np.float64, np.float32]
+EW = ["copy", "mul", "add", "triad", "nstream"]
+SIZES = [1, 2, 3, 5, 31, 32, 33, 255, 1000, 4097, 65536 + 7, (1 << 20) + 3]
+
+
+def tdtype(dt):
+    return torch.float64 if np.dtype(dt) == np.float64 else torch.float32
+
+
+def same_bits(x, y):
+    u = np.uint32 if x.dtype == np.float32 else np.uint64
+    return np.array_equal(np.ascontiguousarray(x).view(u), np.ascontiguousarray(y).view(u))
+
+
+def rand(n, dtype, seed):
+    rng = np.random.default_rng(seed)
+    return (rng.standard_normal(n) * np.exp(rng.uniform(-4, 4, n))).astype(dtype)
+
+
+def oracle_apply(orc, kern, a, b, c, contract):
+    if kern == "copy": orc.copy(a, c)
+    elif kern == "mul": orc.mul(b, c)
+    elif kern == "add": orc.add(a, b, c)
+    elif kern == "triad": orc.triad(a, b, c, contract=contract)
+    elif kern == "nstream": orc.nstream(a, b, c, contract=contract)
+    elif kern == "init": orc.init(a, b, c)
+
+
+def gpu_apply(kern, a0, b0, c0, cfg=None, offset=(0, 0, 0), pad=16):
+    """Run one kernel on device copies placed `offset` elements into padded buffers; returns host results
+    plus the untouched padding (to catch out-of-bounds writes)."""
+    n, dt = a0.size, a0.dtype
+    dev = []
+    for x, off in zip((a0, b0, c0), offset):
+        buf = torch.full((n + 2 * pad + 8,), 7.0, dtype=tdtype(dt), device="cuda")
+        view = buf[pad + off: pad + off + n]
+        view.copy_(torch.from_numpy(x))
+        dev.append((buf, view, pad + off))
+    st = torch.cuda.current_stream().cuda_stream
+    bs.launch(kern, dev[0][1].data_ptr(), dev[1][1].data_ptr(), dev[2][1].data_ptr(), n, dt.itemsize, cfg=cfg, stream=st)
+    torch.cuda.synchronize()
+    outs = []
+    for buf, view, start in dev:
+        full = buf.cpu().numpy()
+        assert (full[:start] == 7.0).all() and (full[start + n:] == 7.0).all(), "kernel wrote outside its array"
+        outs.append(full[start:start + n].copy())
+    return outs
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("kern", EW + ["init"])
+def test_elementwise_auto_cfg_bit_exact(orc, kern, dtype):
+    for n in SIZES:
+        for contract in (True, False):
+            a0, b0, c0 = rand(n, dtype, n), rand(n, dtype, n + 1), rand(n, dtype, n + 2)
+            a, b, c = a0.copy(), b0.copy(), c0.copy()
+            oracle_apply(orc, kern, a, b, c, contract)
+            ga, gb, gc = gpu_apply(kern, a0, b0, c0, cfg=bs.LaunchCfg.make(contract=contract))
+            assert same_bits(ga, a) and same_bits(gb, b) and same_bits(gc, c), (kern, n, contract)
+
+
+CFG_GRID = [dict(vec_bytes=v, unroll=u, cache_hint=h, block=blk, grid=g)
+            for v, us in ((16, (1, 2, 4, 8)), (32, (1, 2, 4))) for u in us
+            for h in (1, 2, 3, 4, 5) for blk, g in ((128, 0), (256, -2), (512, 3))]
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("kern", EW + ["init"])
+def test_elementwise_every_compiled_variant(orc, kern, dtype):
+    """All (vector width, unroll, cache hint) instantiations x three grid shapes, ragged n."""
+    n = 50021
+    a0, b0, c0 = rand(n, dtype, 1), rand(n, dtype, 2), rand(n, dtype, 3)
+    want = {}
+    for contract in (True, False):
+        a, b, c = a0.copy(), b0.copy(), c0.copy()
+        oracle_apply(orc, kern, a, b, c, contract)
+        want[contract] = (a, b, c)
+    for kw in CFG_GRID:
+        for contract in ((True, False) if kern in ("triad", "nstream") else (True,)):
+            ga, gb, gc = gpu_apply(kern, a0, b0, c0, cfg=bs.LaunchCfg.make(contract=contract, **kw))
+            a, b, c = want[contract]
+            assert same_bits(ga, a) and same_bits(gb, b) and same_bits(gc, c), (kern, kw, contract)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("kern", EW)
+def test_elementwise_misaligned_pointers(orc, kern, dtype):
+    """Congruent offsets take the vector path with a scalar head; incongruent ones the scalar fallback."""
+    n = 10007
+    a0, b0, c0 = rand(n, dtype, 4), rand(n, dtype, 5), rand(n, dtype, 6)
+    a, b, c = a0.copy(), b0.copy(), c0.copy()
+    oracle_apply(orc, kern, a, b, c, True)
+    for offset in [(1, 1, 1), (3, 3, 3), (1, 2, 3), (0, 1, 0), (2, 0, 5)]:
+        for vec in (16, 32):
+            ga, gb, gc = gpu_apply(kern, a0, b0, c0, cfg=bs.LaunchCfg.make(vec_bytes=vec), offset=offset)
+            assert same_bits(ga, a) and same_bits(gb, b) and same_bits(gc, c), (kern, offset, vec)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("variant", ["bulk", "tma"])
+def test_copy_async_variants_bit_exact(variant, dtype):
+    """cp.async.bulk and TMA-tensor copy: sizes around the chunk / row boundaries, several ring shapes."""
+    eb = np.dtype(dtype).itemsize
+    for stages, chunk in ((2, 2048), (4, 32768), (3, 16384), (8, 8192)):
+        for nbytes in (8, 2048, 2048 * 3 + 16, chunk - 8, chunk, chunk + 8, 5 * chunk + 2048 + 24,
+                       37 * chunk + 1024, (1 << 22) + 4096 + 8):
+            n = max(1, nbytes // eb)
+            a0 = rand(n, dtype, nbytes % 1000)
+            junk = rand(n, dtype, 99)
+            _, _, gc = gpu_apply("copy", a0, junk, junk, cfg=bs.LaunchCfg.make(variant=variant, stages=stages, chunk_bytes=chunk, grid=-1))
+            assert same_bits(gc, a0), (variant, stages, chunk, n)
+    # a misaligned pointer silently takes the register path and is still exact
+    a0 = rand(5001, dtype, 3)
+    _, _, gc = gpu_apply("copy", a0, a0, a0, cfg=bs.LaunchCfg.make(variant=variant), offset=(1, 0, 1))
+    assert same_bits(gc, a0)
+
+
+def gpu_dot(a0, b0, cfg=None, repeats=1):
+    n, dt = a0.size, a0.dtype
+    a = torch.from_numpy(a0).cuda()
+    b = torch.from_numpy(b0).cuda()
+    ws = torch.zeros(bs.dot_workspace_bytes(), dtype=torch.uint8, device="cuda")
+    out = torch.full((1,), float("nan"), dtype=tdtype(dt), device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    res = []
+    for _ in range(repeats):
+        out.fill_(float("nan"))
+        bs.launch_dot(a.data_ptr(), b.data_ptr(), n, dt.itemsize, ws.data_ptr(), out.data_ptr(), cfg=cfg, stream=st)
+        torch.cuda.synchronize()
+        res.append(out.cpu().numpy()[0])
+    assert int(ws.cpu().numpy().view(np.uint32)[-64:].sum()) == 0, "dot must leave its ticket zeroed"
+    return res
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_dot_tolerance_and_determinism(orc, dtype):
+    eps = np.finfo(dtype).eps
+    for n in SIZES + [(1 << 22) + 11]:
+        a0, b0 = np.abs(rand(n, dtype, n)), np.abs(rand(n, dtype, n + 9))
+        exact = math.fsum(float(x) * float(y) for x, y in zip(a0[:200000], b0[:200000])) if n <= 200000 else \
+            float(np.dot(a0.astype(np.float64), b0.astype(np.float64)))
+        serial = float(orc.dot(a0, b0, contract=True))
+        for contract in (True, False):
+            r = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(contract=contract), repeats=3)
+            assert r[0].tobytes() == r[1].tobytes() == r[2].tobytes(), "dot is not run-to-run deterministic"
+            got = float(r[0])
+            # the reference's own bar, src/main.cpp:384 ...
+            assert abs(got - serial) <= 1e7 * eps * max(abs(got), abs(serial))
+            # ... and the honest one: a tree reduction of positive terms is good to a few eps*log2(n)
+            assert abs(got - exact) <= 4 * eps * max(4.0, math.log2(n)) * abs(exact), (n, got, exact)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_dot_variants_agree_bitwise(dtype):
+    """two_pass and ticket run the same second pass: identical bits; every compiled shape is sane."""
+    n = 300007
+    a0, b0 = rand(n, dtype, 1), rand(n, dtype, 2)
+    exact = float(np.dot(a0.astype(np.float64), b0.astype(np.float64)))
+    scale = float(np.dot(np.abs(a0).astype(np.float64), np.abs(b0).astype(np.float64)))
+    eps = np.finfo(dtype).eps
+    for v, us in ((16, (1, 2, 4, 8)), (32, (1, 2, 4))):
+        for u in us:
+            for h in (1, 2, 3, 4, 5):
+                for blk, g in ((256, -2), (512, 7), (1024 if v * u < 128 else 512, -1)):
+                    kw = dict(vec_bytes=v, unroll=u, cache_hint=h, block=blk, grid=g)
+                    r1 = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(variant="two_pass", **kw))[0]
+                    r2 = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(variant="ticket", **kw))[0]
+                    assert r1.tobytes() == r2.tobytes(), kw
+                    assert abs(float(r1) - exact) <= 8 * eps * 20 * scale, kw
+
+
+def test_dot_misaligned_and_empty(orc):
+    for dtype in DTYPES:
+        n = 7001
+        a0, b0 = np.abs(rand(n, dtype, 1)), np.abs(rand(n, dtype, 2))
+        at = torch.from_numpy(np.concatenate([np.zeros(3, dtype), a0])).cuda()
+        bt = torch.from_numpy(np.concatenate([np.zeros(3, dtype), b0])).cuda()
+        ws = torch.zeros(bs.dot_workspace_bytes(), dtype=torch.uint8, device="cuda")
+        out = torch.zeros(1, dtype=tdtype(dtype), device="cuda")
+        st = torch.cuda.current_stream().cuda_stream
+        for off_a, off_b in ((3, 3), (1, 1), (1, 2), (0, 3)):
+            bs.launch_dot(at[off_a:].data_ptr(), bt[off_b:].data_ptr(), n - 3, a0.itemsize, ws.data_ptr(), out.data_ptr(), stream=st)
+            torch.cuda.synchronize()
+            want = float(np.dot(at[off_a:off_a + n - 3].cpu().numpy().astype(np.float64), bt[off_b:off_b + n - 3].cpu().numpy().astype(np.float64)))
+            assert abs(float(out.item()) - want) <= 64 * np.finfo(dtype).eps * abs(want) + 1e-30
+        bs.launch_dot(at.data_ptr(), bt.data_ptr(), 0, a0.itemsize, ws.data_ptr(), out.data_ptr(), stream=st)
+        torch.cuda.synchronize()
+        assert float(out.item()) == 0.0
+
+
+def test_elementwise_n_zero_is_a_no_op():
+    t = torch.ones(8, dtype=torch.float64, device="cuda")
+    for k in EW + ["init"]:
+        bs.launch(k, t.data_ptr(), t.data_ptr(), t.data_ptr(), 0, 8)
+    torch.cuda.synchronize()
+    assert (t == 1).all()
+
+
+def test_bad_arguments_raise():
+    t = torch.ones(64, dtype=torch.float64, device="cuda")
+    with pytest.raises(bs.B200Error):
+        bs.launch("triad", t.data_ptr(), t.data_ptr(), t.data_ptr(), 64, 2)  # elem_bytes
+    with pytest.raises(bs.B200Error):
+        bs.launch("triad", t.data_ptr(), t.data_ptr(), t.data_ptr(), 64, 8, cfg=bs.LaunchCfg.make(vec_bytes=64))
+    with pytest.raises(bs.B200Error):
+        bs.launch("triad", t.data_ptr(), t.data_ptr(), t.data_ptr(), 64, 8, cfg=bs.LaunchCfg.make(unroll=3))
+    with pytest.raises(bs.B200Error):
+        bs.launch("triad", t.data_ptr(), t.data_ptr(), t.data_ptr(), 64, 8, cfg=bs.LaunchCfg.make(variant="tma"))
+    with pytest.raises(bs.B200Error):
+        bs.launch("triad", 0, t.data_ptr(), t.data_ptr(), 64, 8)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_golden_random_fixture_on_gpu(golden_random, dtype):
+    """The committed reference outputs (tests/golden/random_vectors.npz) straight against the CUDA path."""
+    tag = np.dtype(dtype).name
+    a0, b0, c0 = (golden_random[f"{tag}/in/{k}"] for k in "abc")
+    for mode, contract in (("fast", True), ("off", False)):
+        for kern in EW:
+            ga, gb, gc = gpu_apply(kern, a0, b0, c0, cfg=bs.LaunchCfg.make(contract=contract))
+            for name, got in (("a", ga), ("b", gb), ("c", gc)):
+                assert same_bits(got, golden_random[f"{tag}/{mode}/{kern}/{name}"]), (kern, mode, name)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_full_size_properties(dtype):
+    """BASELINE config size (2^25): size-independent properties instead of a CPU replay.
+    copy is the identity; mul by 1 is the identity; add is commutative; triad(s=0) copies b;
+    nstream(s) == a + triad(s); dot(a, 1) equals the tree sum in float64 within tolerance."""
+    n = 1 << 25
+    eb = np.dtype(dtype).itemsize
+    g = torch.Generator(device="cuda").manual_seed(7)
+    a = torch.randn(n, dtype=tdtype(dtype), device="cuda", generator=g)
+    b = torch.randn(n, dtype=tdtype(dtype), device="cuda", generator=g)
+    c = torch.empty_like(a)
+    st = torch.cuda.current_stream().cuda_stream
+    bs.launch("copy", a.data_ptr(), 0, c.data_ptr(), n, eb, stream=st)
+    assert torch.equal(c, a)
+    b2 = torch.empty_like(a)
+    bs.launch("mul", 0, b2.data_ptr(), a.data_ptr(), n, eb, scalar=1.0, stream=st)
+    assert torch.equal(b2, a)
+    c2 = torch.empty_like(a)
+    bs.launch("add", a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, stream=st)
+    bs.launch("add", b.data_ptr(), a.data_ptr(), c2.data_ptr(), n, eb, stream=st)
+    assert torch.equal(c, c2) and torch.equal(c, a + b)
+    t = torch.empty_like(a)
+    bs.launch("triad", t.data_ptr(), b.data_ptr(), a.data_ptr(), n, eb, scalar=0.0, stream=st)
+    assert torch.equal(t, b)
+    s = 0.4
+    bs.launch("triad", t.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, scalar=s, stream=st)   # t = b + s*c
+    a2 = a.clone()
+    bs.launch("nstream", a2.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, scalar=s, stream=st)  # a2 = a + (b + s*c)
+    assert torch.equal(a2, a + t)
+    # fused triad against torch's own fma-free arithmetic: at most 1 ulp apart, and exactly addcmul in fp64
+    ws = torch.zeros(bs.dot_workspace_bytes(), dtype=torch.uint8, device="cuda")
+    out = torch.zeros(1, dtype=tdtype(dtype), device="cuda")
+    ones = torch.ones_like(a)
+    a_abs = a.abs()
+    bs.launch_dot(a_abs.data_ptr(), ones.data_ptr(), n, eb, ws.data_ptr(), out.data_ptr(), stream=st)
+    want = a_abs.double().sum().item()
+    assert abs(out.item() - want) <= 64 * np.finfo(dtype).eps * want

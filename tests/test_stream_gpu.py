@@ -1,0 +1,236 @@
+"""GPU parity tests, LEVEL 2 of the C ABI: the Stream<T> object, driven the way src/main.cpp drives a model,
+against (1) the committed known answers of the unmodified reference serial model, (2) the oracle's
+check_solution, and (3) the b200-stream binary = reference main.cpp + our model, when it was built."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import babelstream_b200 as bs
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "build", "b200-stream")
+ORDER = ["copy", "mul", "add", "triad", "dot", "nstream"]  # src/benchmark.h:32-39
+
+
+def bits(x):
+    x = np.asarray(x)
+    return ("0x%08x" % int(x.view(np.uint32))) if x.dtype == np.float32 else ("0x%016x" % int(x.view(np.uint64)))
+
+
+def drive(stream, orc, selection, order, num_times):
+    """The loop of src/main.cpp:150-180 over a B200Stream."""
+    total = stream.dtype.type(0)
+    outer, inner = (num_times, 6) if order == O.ORDER_CLASSIC else (6, num_times)
+    for o in range(outer):
+        for i in range(inner):
+            pos = i if order == O.ORDER_CLASSIC else o
+            if not orc.run_benchmark(selection, pos):
+                continue
+            r = stream.run(ORDER[pos])
+            if ORDER[pos] == "dot":
+                total = r
+    return total
+
+
+def test_known_answers_every_row(orc, golden_rows):
+    """192 rows: (dtype, selection, order, num_times, contraction) -> a, b, c bit patterns."""
+    streams = {}
+    for r in golden_rows:
+        dt = np.dtype(r["dtype"])
+        key = (r["dtype"], r["contract"])
+        if key not in streams:
+            streams[key] = bs.B200Stream(r["n"], dtype=dt, contract=r["contract"])
+        s = streams[key]
+        s.init_arrays()  # the driver's timed init, src/main.cpp:280
+        order = O.ORDER_CLASSIC if r["order"] == "Classic" else O.ORDER_ISOLATED
+        total = drive(s, orc, O.SELECTIONS[r["selection"]], order, r["num_times"])
+        a, b, c = s.get_arrays()
+        assert (bits(a[0]), bits(b[0]), bits(c[0])) == (r["a"], r["b"], r["c"]), r
+        assert (a == a[0]).all() and (b == b[0]).all() and (c == c[0]).all()
+        want = np.array(int(r["dot"], 16), dtype=np.uint64 if dt == np.float64 else np.uint32).view(dt)
+        if np.isfinite(want) and orc.run_benchmark(O.SELECTIONS[r["selection"]], 4):
+            # serial order differs from the tree: tolerance, but a tight one (all terms equal, n = 1024)
+            assert abs(float(total) - float(want)) <= 16 * np.finfo(dt).eps * abs(float(want)), r
+    for s in streams.values():
+        s.close()
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("n", [1, 100, 33554432 // 32 + 5])
+def test_check_solution_passes(orc, dtype, n):
+    for sel in ("Classic", "All", "Triad", "Nstream", "Dot", "Copy"):
+        for order in (O.ORDER_CLASSIC, O.ORDER_ISOLATED):
+            nt = 4 if dtype is np.float32 and sel == "All" else 10
+            with bs.B200Stream(n, dtype=dtype) as s:
+                s.init_arrays()
+                total = drive(s, orc, O.SELECTIONS[sel], order, nt)
+                a, b, c = s.get_arrays()
+                assert orc.check_solution(O.SELECTIONS[sel], order, nt, a, b, c, total) == 0, (sel, order)
+                # stronger than the reference's 100*eps: bit-exact against the oracle's gold recurrence
+                g = orc.gold(dtype, O.SELECTIONS[sel], order, nt, n)
+                assert bits(a[0]) == bits(g[0]) and bits(b[-1]) == bits(g[1]) and bits(c[n // 2]) == bits(g[2])
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_full_size_all_kernels_bit_exact(orc, dtype):
+    """BASELINE config 2: 2^25 elements, all six kernels; every element compared with the gold bits."""
+    n, nt = 1 << 25, 5
+    with bs.B200Stream(n, dtype=dtype) as s:
+        s.init_arrays()
+        total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, nt)
+        a, b, c = s.get_arrays()
+        g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, nt, n)
+        u = np.uint64 if dtype is np.float64 else np.uint32
+        for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+            assert (arr.view(u) == np.asarray(gold).view(u)).all()
+        assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, nt, a, b, c, total) == 0
+        assert abs(float(total) - float(g[3])) <= 64 * np.finfo(dtype).eps * abs(float(g[3]))
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_write_read_roundtrip_and_random_parity(orc, dtype):
+    n = 100003
+    rng = np.random.default_rng(3)
+    a0, b0, c0 = (rng.standard_normal(n).astype(dtype) for _ in range(3))
+    for contract in ("fast", "off"):
+        with bs.B200Stream(n, dtype=dtype, contract=contract) as s:
+            s.write_arrays(a0, b0, c0)
+            ra, rb, rc = s.read_arrays()
+            assert np.array_equal(ra, a0) and np.array_equal(rb, b0) and np.array_equal(rc, c0)
+            a, b, c = a0.copy(), b0.copy(), c0.copy()
+            for k in ("copy", "mul", "add", "triad", "nstream", "triad", "add"):
+                s.run(k)
+                {"copy": lambda: orc.copy(a, c), "mul": lambda: orc.mul(b, c), "add": lambda: orc.add(a, b, c),
+                 "triad": lambda: orc.triad(a, b, c, contract=(contract == "fast")),
+                 "nstream": lambda: orc.nstream(a, b, c, contract=(contract == "fast"))}[k]()
+            ga, gb, gc = s.get_arrays()
+            u = np.uint64 if dtype is np.float64 else np.uint32
+            assert np.array_equal(ga.view(u), a.view(u)) and np.array_equal(gb.view(u), b.view(u)) and np.array_equal(gc.view(u), c.view(u))
+            d = float(s.dot())
+            want = float(np.dot(a.astype(np.float64), b.astype(np.float64)))
+            scale = float(np.dot(np.abs(a).astype(np.float64), np.abs(b).astype(np.float64)))
+            assert abs(d - want) <= 64 * np.finfo(dtype).eps * scale
+
+
+def test_options_and_variants(orc):
+    n = 1 << 20
+    ref = None
+    for opts in ({}, {"copy_variant": "bulk"}, {"copy_variant": "tma"}, {"dot_variant": "two_pass"},
+                 {"sync": "spin"}, {"timing": "1"}, {"tune": "all:vec=16,unroll=4,hint=3,grid=-4;dot:vec=32,unroll=2,block=256"}):
+        with bs.B200Stream(n, dtype=np.float64, **opts) as s:
+            total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)
+            a, b, c = s.get_arrays()
+            cur = (bits(a[0]), bits(b[0]), bits(c[0]), bits(a[-1]))
+            ref = ref or cur
+            assert cur == ref, opts
+            assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, total) == 0
+            if opts.get("timing"):
+                assert s.last_kernel_ms() > 0
+            else:
+                assert s.last_kernel_ms() < 0
+            assert "triad" in s.describe()
+
+
+def test_constructor_errors():
+    with pytest.raises(bs.B200Error) as e:
+        bs.B200Stream(1024, device=99)
+    assert "Invalid device index" in str(e.value)  # the reference's message, CUDAStream.cu:88
+    with pytest.raises(bs.B200Error) as e:
+        bs.B200Stream(1 << 40, dtype=np.float64)
+    assert "enough memory" in str(e.value)         # CUDAStream.cu:139
+    with pytest.raises(bs.B200Error):
+        bs.B200Stream(0)
+    with pytest.raises(TypeError):
+        bs.B200Stream(16, dtype=np.int32)
+
+
+needs_bin = pytest.mark.skipif(not os.path.exists(BIN), reason="build/b200-stream not built (needs the reference tree)")
+
+
+def run_bin(*args, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    return subprocess.run([BIN, *args], capture_output=True, text=True, timeout=600, env=e)
+
+
+@needs_bin
+def test_driver_ci_sanity_case():
+    """The one run-time check of the reference's CI (src/ci-test-compile.sh:143-147), on our model."""
+    p = run_bin("-s", "1048576", "-n", "10")
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "Implementation: B200" in p.stdout and "Triad" in p.stdout and "FAILED" not in p.stderr
+
+
+@needs_bin
+@pytest.mark.parametrize("args", [
+    ["--float"], ["--only", "Triad"], ["--only", "Nstream"], ["--only", "All"], ["--only", "Dot"],
+    ["--order", "Isolated"], ["--only", "All", "--order", "Isolated", "--float", "-n", "4"], ["-s", "1000003"],
+    ["-s", "1", "-n", "2"],
+])
+def test_driver_cli_matrix(args):
+    """CLI flags of src/main.cpp:423-603 reach the model unchanged; check_solution decides the exit code."""
+    base = [] if "-s" in args else ["-s", "2097152"]
+    base += [] if "-n" in args else ["-n", "10"]
+    p = run_bin(*base, *args)
+    assert p.returncode == 0, p.stdout + p.stderr
+
+
+@needs_bin
+def test_driver_csv_and_contract_off():
+    p = run_bin("-s", "4194304", "-n", "20", "--csv", "--only", "All", env={"BABELSTREAM_B200_CONTRACT": "off"})
+    assert p.returncode == 0, p.stdout + p.stderr
+    rows = [l.split(",") for l in p.stdout.splitlines() if l and l.split(",")[0] in ("Copy", "Mul", "Add", "Triad", "Dot", "Nstream")]
+    assert [r[0] for r in rows] == ["Copy", "Mul", "Add", "Triad", "Dot", "Nstream"]
+    assert all(int(r[2]) == 4194304 and int(r[3]) == 8 and float(r[4]) > 0 for r in rows)
+    header = [l for l in p.stdout.splitlines() if l.startswith("function,")]
+    assert header and header[0].split(",")[4] == "max_MB_per_sec"
+
+
+@needs_bin
+def test_driver_list_and_bad_device():
+    p = run_bin("--list")
+    assert p.returncode == 0 and "0:" in p.stdout
+    p = run_bin("--device", "99", "-s", "1024", "-n", "2")
+    assert p.returncode != 0 and "Invalid device index" in p.stderr
+
+
+multi = pytest.mark.skipif(bs.lib() is None or bs.device_count() < 2, reason="needs >= 2 GPUs")
+
+
+@multi
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("combine", ["nccl", "host"])
+def test_multi_gpu_sharded_bit_exact(orc, dtype, combine):
+    os.environ["BABELSTREAM_B200_DOT_COMBINE"] = combine
+    try:
+        for ngpus in range(2, min(bs.device_count(), 8) + 1):
+            for n in (ngpus - 1, 1000, (1 << 22) + 17):
+                nt = 4
+                with bs.B200Stream(n, dtype=dtype, ngpus=ngpus) as s:
+                    assert s.ngpus == ngpus
+                    total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, nt)
+                    a, b, c = s.get_arrays()
+                    g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, nt, n)
+                    u = np.uint64 if dtype is np.float64 else np.uint32
+                    for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+                        assert (arr.view(u) == np.asarray(gold).view(u)).all(), (ngpus, n)
+                    assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, nt, a, b, c, total) == 0
+                    assert abs(float(total) - float(g[3])) <= 64 * np.finfo(dtype).eps * abs(float(g[3]))
+                    t2 = s.dot()
+                    t3 = s.dot()
+                    assert t2.tobytes() == t3.tobytes()
+    finally:
+        os.environ.pop("BABELSTREAM_B200_DOT_COMBINE", None)
+
+
+@multi
+@needs_bin
+def test_driver_multi_gpu():
+    p = run_bin("-s", str((1 << 24) + 3), "-n", "10", "--only", "All", env={"BABELSTREAM_B200_NGPUS": "2"})
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "GPUs: 2" in p.stdout
