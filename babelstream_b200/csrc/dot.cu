@@ -36,7 +36,8 @@ static int launch_dot_typed(const DotCall& call) {
   count_launch();
   B200_CUDA(cudaPeekAtLastError());
   if (!TICKET) {
-    dot_final_kernel<T><<<1, 1024, 0, call.stream>>>(static_cast<const T*>(call.workspace), call.grid,
+    // same block size as pass 1, so that both variants add the partials in the same order
+    dot_final_kernel<T><<<1, call.r.block, 0, call.stream>>>(static_cast<const T*>(call.workspace), call.grid,
                                                       static_cast<T*>(call.result_dev),
                                                       static_cast<T*>(call.result_host));
     count_launch();

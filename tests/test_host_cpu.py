@@ -1,0 +1,224 @@
+"""CPU tests (no GPU, no compute calls): the C ABI loads and exports every declared symbol, the host
+logic behind it (shard partition, launch-shape resolution, error behaviour), the build glue, and the
+N > 1 plumbing with world_size-2 gloo."""
+import os
+import re
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import babelstream_b200 as bs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200_stream.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = declared_symbols()
+    assert len(names) >= 35 and "b200_launch_triad" in names and "b200_create" in names
+    L = bs.lib()
+    missing = [n for n in names if not hasattr(L, n)]
+    assert not missing, missing
+    assert b"sm_100a" in L.b200_version()
+
+
+def test_python_binding_covers_the_header():
+    """stream.py binds (argtypes/restype) every function the header declares."""
+    L = bs.lib()
+    unbound = [n for n in declared_symbols() if getattr(L, n).argtypes is None]
+    assert not unbound, unbound
+
+
+@pytest.mark.skipif(bs.device_count() > 0, reason="only meaningful on a machine without a GPU")
+def test_no_cpu_fallback():
+    with pytest.raises(bs.B200Error) as e:
+        bs.B200Stream(1024)
+    assert e.value.code == -2 and "no CPU fallback" in str(e.value)
+    with pytest.raises(bs.B200Error):
+        bs.launch("triad", 64, 64, 64, 16, 8)
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    import babelstream_b200.stream as st
+    monkeypatch.setattr(st, "_lib", None)
+    monkeypatch.setenv("BABELSTREAM_B200_LIB", "/nonexistent/libb200stream.so")
+    with pytest.raises(bs.B200Error) as e:
+        st.lib()
+    assert "no CPU fallback" in str(e.value)
+    monkeypatch.delenv("BABELSTREAM_B200_LIB")
+    monkeypatch.setattr(st, "_lib", None)
+    assert st.lib() is not None
+
+
+@pytest.mark.parametrize("elem_bytes", [4, 8])
+def test_shard_range_partitions_exactly(elem_bytes):
+    align = 128 // elem_bytes
+    for n in [1, 2, 15, 16, 17, 1000, 4097, 1 << 20, (1 << 25) + 3, 1 << 31, (1 << 33) + 5]:
+        for g in range(1, 9):
+            pos = 0
+            sizes = []
+            for r in range(g):
+                b, c = bs.shard_range(n, elem_bytes, g, r)
+                assert b == pos, "shards must be contiguous and in rank order"
+                assert b % align == 0 or c == 0, "every non-empty shard starts on a 128-byte boundary"
+                pos += c
+                sizes.append(c)
+            assert pos == n
+            assert max(sizes) - min(s for s in sizes if s or True) <= max(sizes)  # trailing shards may be short
+            if n % (g * align) == 0:
+                assert len(set(sizes)) == 1, "divisible sizes split evenly (all BASELINE configs are powers of two)"
+    with pytest.raises(bs.B200Error):
+        bs.shard_range(10, 8, 0, 0)
+    with pytest.raises(bs.B200Error):
+        bs.shard_range(10, 8, 2, 2)
+    with pytest.raises(bs.B200Error):
+        bs.shard_range(10, 3, 2, 0)
+
+
+def test_resolve_cfg_defaults_and_overrides():
+    big, grid = bs.resolve_cfg("triad", 1 << 29, 8)
+    assert big.variant == bs.VARIANTS["ldst"] and big.contract == 1 and big.cache_hint != bs.HINTS["default"]
+    tile = big.block * big.unroll * (big.vec_bytes // 8)
+    assert grid == ((1 << 29) + tile - 1) // tile or grid % 148 == 0
+    small, _ = bs.resolve_cfg("triad", 1 << 20, 8)   # 3 x 8 MB lives in the 126 MB L2
+    assert small.cache_hint == bs.HINTS["default"], "no evict-first / no-allocate hints for an L2-resident working set"
+    dot, grid = bs.resolve_cfg("dot", 1 << 25, 8)
+    assert dot.variant in (1, 2) and 0 < grid <= 4096 and grid % 148 == 0
+    o, grid = bs.resolve_cfg("copy", 1 << 25, 4, cfg=bs.LaunchCfg.make(vec_bytes=16, unroll=8, block=128, grid=-3,
+                                                                      cache_hint="stream", variant="bulk", contract="off"))
+    assert (o.vec_bytes, o.unroll, o.block, o.grid, o.cache_hint, o.variant, o.contract) == (16, 8, 128, -3, 4, 2, 2)
+    assert grid == 3 * 148
+    _, grid = bs.resolve_cfg("add", 1000, 8, num_sms=148, cfg=bs.LaunchCfg.make(grid=-8))
+    assert grid == 2, "never more blocks than tiles (500 16-byte vectors / 256 threads = 2 tiles)"
+    scalar, _ = bs.resolve_cfg("mul", 1000, 8, cfg=bs.LaunchCfg.make(vec_bytes=8))
+    assert scalar.unroll == 4 and scalar.cache_hint == 1
+
+
+@pytest.mark.parametrize("bad", [dict(vec_bytes=24), dict(unroll=3), dict(unroll=8, vec_bytes=32), dict(block=100),
+                                 dict(block=1024), dict(cache_hint=9), dict(contract=5)])
+def test_resolve_cfg_rejects(bad):
+    with pytest.raises(bs.B200Error):
+        bs.resolve_cfg("triad", 1 << 20, 8, cfg=bs.LaunchCfg.make(**bad))
+
+
+def test_resolve_cfg_kernel_specific_rules():
+    with pytest.raises(bs.B200Error):
+        bs.resolve_cfg("triad", 1 << 20, 8, cfg=bs.LaunchCfg.make(variant="tma"))   # only copy has async variants
+    bs.resolve_cfg("copy", 1 << 20, 8, cfg=bs.LaunchCfg.make(variant="tma"))
+    bs.resolve_cfg("dot", 1 << 20, 8, cfg=bs.LaunchCfg.make(block=1024, vec_bytes=16, unroll=2))
+    with pytest.raises(bs.B200Error):
+        bs.resolve_cfg("dot", 1 << 20, 2)
+
+
+def test_gen_stream_models_inserts_exactly_the_b200_branch():
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gen_stream_models as g
+    fake = ('#pragma once\n#include <memory>\n\n#if defined(CUDA)\n#include "CUDAStream.h"\n#elif defined(OMP)\n#include "OMPStream.h"\n#endif\n\n'
+            'template <typename T, typename...Args>\nstd::unique_ptr<Stream<T>> make_stream(Args... args) {\n#if defined(CUDA)\n'
+            '  // Use the CUDA implementation\n  return std::make_unique<CUDAStream<T>>(args...);\n#else\n  #error unknown benchmark\n#endif\n}\n')
+    out = g.transform(fake)
+    assert out.count("B200Stream") == 2 and out.count("defined(B200)") == 2
+    # removing the inserted lines gives the input back: nothing else changed
+    stripped = out.replace('#if defined(B200)\n#include "B200Stream.h"\n#elif defined(CUDA)', "#if defined(CUDA)")
+    stripped = stripped.replace("#if defined(B200)\n  // Use the B200 (sm_100a) implementation\n  return std::make_unique<B200Stream<T>>(args...);\n\n#elif defined(CUDA)", "#if defined(CUDA)")
+    assert stripped == fake
+    with pytest.raises(SystemExit):
+        g.transform("nothing to anchor on")
+    ref = "/root/reference/src/StreamModels.h"
+    if os.path.exists(ref):
+        real = g.transform(open(ref).read())
+        assert real.count("B200Stream") == 2 and "CUDAStream" in real and "SerialStream" in real
+
+
+def test_bench_csv_parser_and_step_metric():
+    sys.path.insert(0, ROOT)
+    import bench
+    text = ("BabelStream\nfunction,num_times,n_elements,sizeof,max_GB_per_sec,min_runtime,max_runtime,avg_runtime\n"
+            "Copy,100,1024,8,10.0,0.001,0.002,0.0015\nMul,100,1024,8,10.0,0.001,0.002,0.0015\nAdd,100,1024,8,10.0,0.001,0.002,0.0015\n"
+            "Triad,100,1024,8,12.5,0.001,0.002,0.0015\nDot,100,1024,8,10.0,0.001,0.002,0.0015\nNstream,100,1024,8,10.0,0.001,0.002,0.0015\n")
+    rows = bench.parse_stream_csv(text)
+    assert list(rows) == ["copy", "mul", "add", "triad", "dot", "nstream"] and rows["triad"]["gbs"] == 12.5
+    gbs, t = bench.step_gbs_from_csv(rows, 1024)
+    assert abs(t - 0.009) < 1e-12 and abs(gbs - 16 * 8 * 1024 / 0.009 / 1e9) < 1e-12
+    assert bench.STEP_WEIGHT == 16 and bench.WEIGHT == {k: bs.WEIGHTS[k] for k in bench.KERNEL_ORDER}
+    assert bench.KERNEL_ORDER == bs.KERNELS
+
+
+# ---- N > 1 on CPU: world_size 2, gloo -----------------------------------------------------------------
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _rank_main(rank, world, port, n, q):
+    """What one rank of the sharded path does, with the oracle standing in for the GPU kernels:
+    its contiguous shard, no data-path collective for the elementwise kernels, ONE all-reduce of one
+    element for dot, and the max-over-ranks reduction bench.py uses for timing."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    import oracle as O
+    import babelstream_b200 as bsx
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    orc = O.Oracle()
+    begin, count = bsx.shard_range(n, 8, world, rank)
+    a, b, c = (np.empty(count, dtype=np.float64) for _ in range(3))
+    orc.init(a, b, c)
+    total = None
+    for _ in range(3):
+        orc.copy(a, c); orc.mul(b, c); orc.add(a, b, c); orc.triad(a, b, c)
+        part = torch.tensor([float(orc.dot(a, b))], dtype=torch.float64)
+        dist.all_reduce(part)                      # the path's only exchange step
+        total = part.item()
+        orc.nstream(a, b, c)
+    ms = torch.tensor([10.0 + rank], dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)      # timing: max over ranks
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (begin, count, a.tobytes(), b.tobytes(), c.tobytes()))
+    if rank == 0:
+        q.put((total, ms.item(), gathered))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharded_path_matches_unsharded_oracle(orc):
+    import torch.multiprocessing as mp
+    import oracle as O
+    n, world = 100003, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rank_main, args=(r, world, port, n, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    total, ms, gathered = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert ms == 11.0
+    a, b, c = (np.empty(n, dtype=np.float64) for _ in range(3))
+    orc.init(a, b, c)
+    want = None
+    for _ in range(3):
+        orc.copy(a, c); orc.mul(b, c); orc.add(a, b, c); orc.triad(a, b, c)
+        want = float(orc.dot(a, b))
+        orc.nstream(a, b, c)
+    pos = 0
+    for begin, count, ra, rb, rc in gathered:
+        assert begin == pos
+        for full, raw in ((a, ra), (b, rb), (c, rc)):
+            assert np.array_equal(full[begin:begin + count].view(np.uint64), np.frombuffer(raw, dtype=np.uint64))
+        pos += count
+    assert pos == n
+    assert abs(total - want) <= 1e7 * np.finfo(np.float64).eps * abs(want)   # src/main.cpp:384
+    assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, np.float64(total)) == 0
