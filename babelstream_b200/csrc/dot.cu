@@ -5,6 +5,7 @@
 namespace b200 {
 
 #define B200_DOT_FOR_HINT(H)                                                                      \
+  B200_DOT_CASE(8, 1, H) B200_DOT_CASE(8, 2, H) B200_DOT_CASE(8, 4, H)                            \
   B200_DOT_CASE(16, 1, H) B200_DOT_CASE(16, 2, H) B200_DOT_CASE(16, 4, H) B200_DOT_CASE(16, 8, H) \
   B200_DOT_CASE(32, 1, H) B200_DOT_CASE(32, 2, H) B200_DOT_CASE(32, 4, H)
 
@@ -16,7 +17,7 @@ static int launch_dot_typed(const DotCall& call) {
 #define B200_DOT_CASE(VB, U, H) \
   if (vb == VB && u == U && h == H) k = dot_kernel<T, VB, U, H, FUSED, TICKET>;
   B200_DOT_FOR_HINT(1) B200_DOT_FOR_HINT(2) B200_DOT_FOR_HINT(3) B200_DOT_FOR_HINT(4) B200_DOT_FOR_HINT(5)
-  if (vb == (int)sizeof(T) && u == 4 && h == 1) k = dot_kernel<T, (int)sizeof(T), 4, 1, FUSED, TICKET>;
+  if constexpr (sizeof(T) == 4) { if (vb == 4 && u == 4 && h == 1) k = dot_kernel<T, 4, 4, 1, FUSED, TICKET>; }
 #undef B200_DOT_CASE
   if (!k) {
     set_error("no dot kernel compiled for vec_bytes=%d unroll=%d cache_hint=%d", vb, u, h);

@@ -218,8 +218,12 @@ __device__ __forceinline__ void ew_scalar(T* a, T* b, T* c, unsigned long long i
   else if constexpr (OP == OP_NSTREAM) a[i] = add_rn(a[i], axpy<FUSED>(s0, c[i], b[i]));
 }
 
+// Threads per block the register budget allows: up to 32 bytes per thread per array fit in the 64
+// registers of a 1024-thread block; wider tiles run with at most 512 threads (128 registers).
+constexpr int ew_max_block(int vb, int unroll) { return vb * unroll <= 32 ? 1024 : 512; }
+
 template <typename T, int OP, int VB, int UNROLL, int HINT, bool FUSED>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(ew_max_block(VB, UNROLL))
 ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
   constexpr int EPV = VB / (int)sizeof(T);
   constexpr bool LA = (OP == OP_COPY || OP == OP_ADD || OP == OP_NSTREAM);

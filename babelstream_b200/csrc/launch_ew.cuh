@@ -8,9 +8,11 @@
 namespace b200 {
 
 // The compiled variant space per (T, op, rounding):
-//   16-byte vectors: unroll 1 2 4 8      32-byte vectors: unroll 1 2 4      x  5 cache hints
-//   scalar fallback (misaligned operands): unroll 4, default hint
-#define B200_EW_FOR_HINT(H)                     \
+//   8-byte: unroll 1 2 4     16-byte: unroll 1 2 4 8     32-byte: unroll 1 2 4      x  5 cache hints
+//   float scalar fallback (misaligned operands): 4-byte accesses, unroll 4, default hint
+//   (the double scalar fallback is the 8-byte, unroll 4, default-hint member of the table)
+#define B200_EW_FOR_HINT(H)                                                                   \
+  B200_EW_CASE(8, 1, H) B200_EW_CASE(8, 2, H) B200_EW_CASE(8, 4, H)                           \
   B200_EW_CASE(16, 1, H) B200_EW_CASE(16, 2, H) B200_EW_CASE(16, 4, H) B200_EW_CASE(16, 8, H) \
   B200_EW_CASE(32, 1, H) B200_EW_CASE(32, 2, H) B200_EW_CASE(32, 4, H)
 
@@ -22,11 +24,15 @@ int launch_ew_typed(const EwCall& call) {
 #define B200_EW_CASE(VB, U, H) \
   if (vb == VB && u == U && h == H) k = ew_kernel<T, OP, VB, U, H, FUSED>;
   B200_EW_FOR_HINT(1) B200_EW_FOR_HINT(2) B200_EW_FOR_HINT(3) B200_EW_FOR_HINT(4) B200_EW_FOR_HINT(5)
-  if (vb == (int)sizeof(T) && u == 4 && h == 1) k = ew_kernel<T, OP, (int)sizeof(T), 4, 1, FUSED>;
+  if constexpr (sizeof(T) == 4) { if (vb == 4 && u == 4 && h == 1) k = ew_kernel<T, OP, 4, 4, 1, FUSED>; }
 #undef B200_EW_CASE
   if (!k) {
     set_error("no elementwise kernel compiled for vec_bytes=%d unroll=%d cache_hint=%d", vb, u, h);
     return B200_EUNSUPPORTED;
+  }
+  if (call.r.block > ew_max_block(vb, u)) {
+    set_error("block %d too large for vec_bytes=%d unroll=%d (max %d)", call.r.block, vb, u, ew_max_block(vb, u));
+    return B200_EINVAL;
   }
   EwArgs args;
   args.a = call.a; args.b = call.b; args.c = call.c;

@@ -52,18 +52,37 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
 
   Resolved r;
   memset(&r, 0, sizeof r);
-  // ---- defaults (auto) ----
-  if (kernel == B200_DOT) {
-    r.vec_bytes = 16; r.unroll = 4; r.block = tiny ? 256 : 512;
-    r.grid_policy = tiny ? -2 : -4;            // blocks per SM, grid-stride
-    r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
-    r.variant = B200_VARIANT_DOT_TICKET;
-  } else {
-    r.vec_bytes = tiny ? 16 : 32; r.unroll = tiny ? 1 : 2; r.block = 256;
-    r.grid_policy = INT_MAX;                   // one tile per block
-    r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
-    r.variant = B200_VARIANT_LDST;
+  // ---- defaults (auto): winners of tools/sweep.py on B200, profiles/r01/sweep_f64.csv --------
+  // Elementwise kernels: one tile per block always beats a persistent grid-stride loop (by 4-10 %),
+  // and the best tile keeps ~32 bytes of loads in flight per thread at full occupancy -- the
+  // smallest in-flight window that still covers bandwidth x latency (Little's law), which keeps
+  // the DRAM pages touched concurrently few:
+  //     copy, mul      (1 load)   16-byte vectors x unroll 2, 512 threads   6.70 / 6.99 TB/s (2^25 / 2^29 fp64)
+  //     add, triad     (2 loads)  16-byte vectors x unroll 1, 512 threads   7.00 / 7.18-7.24
+  //     nstream        (3 loads)  16-byte vectors x unroll 2, 512 threads   7.16 / 7.33
+  //     init           (stores)   32-byte vectors x unroll 1, 256 threads   7.36 / 7.60
+  // Cache hints differ by < 0.5 %; evict_first wins narrowly beyond L2 and must be OFF for
+  // working sets that fit in L2, where it would destroy the reuse between consecutive kernels.
+  const int stream_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_EVICT_FIRST;
+  r.cache_hint = stream_hint;
+  r.variant = B200_VARIANT_LDST;
+  r.grid_policy = INT_MAX;  // one tile per block
+  switch (kernel) {
+    case B200_COPY: case B200_MUL: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
+    case B200_ADD: case B200_TRIAD: r.vec_bytes = 16; r.unroll = 1; r.block = 512; break;
+    case B200_NSTREAM: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
+    case B200_INIT: r.vec_bytes = 32; r.unroll = 1; r.block = 256; break;
+    case B200_DOT:
+      // read-only: a bounded grid-stride grid (the partials must fit the workspace).  Large inputs
+      // want long tiles on 8 blocks per SM (7.44 TB/s at 2^29); mid sizes a short 2-per-SM grid
+      // whose tail is cheap (6.77 TB/s at 2^25).
+      r.variant = B200_VARIANT_DOT_TICKET;
+      if (bytes_moved >= 2.0 * 1024 * 1024 * 1024) { r.vec_bytes = 32; r.unroll = 4; r.block = 512; r.grid_policy = -8; }
+      else { r.vec_bytes = 16; r.unroll = 8; r.block = 256; r.grid_policy = -2; }
+      r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
+      break;
   }
+  if (tiny && kernel != B200_DOT) { r.block = 256; }  // latency-bound: more, smaller blocks
   r.contract = 1;
   r.stages = 4;
   r.chunk_bytes = 32768;
@@ -80,15 +99,19 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   if (c.chunk_bytes) r.chunk_bytes = c.chunk_bytes;
 
   // ---- validation ----
-  if (r.vec_bytes != 16 && r.vec_bytes != 32 && r.vec_bytes != elem_bytes) {
-    set_error("vec_bytes must be 16, 32 or elem_bytes (scalar), got %d", r.vec_bytes); return B200_EINVAL;
+  if (r.vec_bytes != 8 && r.vec_bytes != 16 && r.vec_bytes != 32 && r.vec_bytes != elem_bytes) {
+    set_error("vec_bytes must be 8, 16, 32 or elem_bytes (scalar), got %d", r.vec_bytes); return B200_EINVAL;
   }
-  if (r.vec_bytes == elem_bytes) { r.unroll = 4; r.cache_hint = B200_HINT_DEFAULT; }
+  if (r.vec_bytes == 4) { r.unroll = 4; r.cache_hint = B200_HINT_DEFAULT; }  // float scalar path: one shape
   const bool unroll_ok = r.unroll == 1 || r.unroll == 2 || r.unroll == 4 || (r.unroll == 8 && r.vec_bytes == 16);
   if (!unroll_ok) { set_error("unroll must be 1, 2, 4 (or 8 with 16-byte vectors), got %d", r.unroll); return B200_EINVAL; }
-  const int max_block = kernel == B200_DOT ? 1024 : 512;
+  // register budget: see ew_max_block / dot_max_block in kernels.cuh
+  const int max_block = kernel == B200_DOT ? (r.vec_bytes * r.unroll >= 128 ? 512 : 1024)
+                                           : (r.vec_bytes * r.unroll <= 32 ? 1024 : 512);
   if (r.block < 32 || r.block > max_block || r.block % 32) {
-    set_error("block must be a multiple of 32 in [32, %d], got %d", max_block, r.block); return B200_EINVAL;
+    set_error("block must be a multiple of 32 in [32, %d] for vec_bytes=%d unroll=%d, got %d", max_block, r.vec_bytes,
+              r.unroll, r.block);
+    return B200_EINVAL;
   }
   if (r.cache_hint < B200_HINT_DEFAULT || r.cache_hint > B200_HINT_PREFETCH) {
     set_error("cache_hint out of range: %d", r.cache_hint); return B200_EINVAL;

@@ -97,12 +97,14 @@ def test_resolve_cfg_defaults_and_overrides():
     assert grid == 3 * 148
     _, grid = bs.resolve_cfg("add", 1000, 8, num_sms=148, cfg=bs.LaunchCfg.make(grid=-8))
     assert grid == 2, "never more blocks than tiles (500 16-byte vectors / 256 threads = 2 tiles)"
-    scalar, _ = bs.resolve_cfg("mul", 1000, 8, cfg=bs.LaunchCfg.make(vec_bytes=8))
-    assert scalar.unroll == 4 and scalar.cache_hint == 1
+    scalar, _ = bs.resolve_cfg("mul", 1000, 4, cfg=bs.LaunchCfg.make(vec_bytes=4))
+    assert scalar.unroll == 4 and scalar.cache_hint == 1, "the float scalar path has one compiled shape"
+    wide, _ = bs.resolve_cfg("triad", 1 << 29, 8, cfg=bs.LaunchCfg.make(block=1024))
+    assert wide.block == 1024, "1024-thread blocks are allowed while vec_bytes*unroll <= 32"
 
 
 @pytest.mark.parametrize("bad", [dict(vec_bytes=24), dict(unroll=3), dict(unroll=8, vec_bytes=32), dict(block=100),
-                                 dict(block=1024), dict(cache_hint=9), dict(contract=5)])
+                                 dict(block=1024, unroll=4), dict(block=2048), dict(cache_hint=9), dict(contract=5)])
 def test_resolve_cfg_rejects(bad):
     with pytest.raises(bs.B200Error):
         bs.resolve_cfg("triad", 1 << 20, 8, cfg=bs.LaunchCfg.make(**bad))

@@ -79,8 +79,8 @@ def test_elementwise_auto_cfg_bit_exact(orc, kern, dtype):
 
 
 CFG_GRID = [dict(vec_bytes=v, unroll=u, cache_hint=h, block=blk, grid=g)
-            for v, us in ((16, (1, 2, 4, 8)), (32, (1, 2, 4))) for u in us
-            for h in (1, 2, 3, 4, 5) for blk, g in ((128, 0), (256, -2), (512, 3))]
+            for v, us in ((8, (1, 2, 4)), (16, (1, 2, 4, 8)), (32, (1, 2, 4))) for u in us
+            for h in (1, 2, 3, 4, 5) for blk, g in ((128, 0), (256, -2), (1024 if v * u <= 32 else 512, 3))]
 
 
 @pytest.mark.parametrize("dtype", DTYPES)
@@ -177,7 +177,7 @@ def test_dot_variants_agree_bitwise(dtype):
     exact = float(np.dot(a0.astype(np.float64), b0.astype(np.float64)))
     scale = float(np.dot(np.abs(a0).astype(np.float64), np.abs(b0).astype(np.float64)))
     eps = np.finfo(dtype).eps
-    for v, us in ((16, (1, 2, 4, 8)), (32, (1, 2, 4))):
+    for v, us in ((8, (1, 2, 4)), (16, (1, 2, 4, 8)), (32, (1, 2, 4))):
         for u in us:
             for h in (1, 2, 3, 4, 5):
                 for blk, g in ((256, -2), (512, 7), (1024 if v * u < 128 else 512, -1)):

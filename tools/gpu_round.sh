@@ -1,0 +1,52 @@
+#!/bin/bash
+# One GPU-box session: parity suite, smoke, both bench arms, ncu evidence, tuning sweeps.
+# Usage (under gpurun): bash tools/gpu_round.sh [tests|bench|ncu|sweep|driver ...]   default: all
+set -u
+mkdir -p gpurun_out
+STAGES="${*:-tests bench ncu sweep driver}"
+has() { [[ " $STAGES " == *" $1 "* ]]; }
+BENCH_SMALL="python bench.py --steps 2 --warmup 3 --no-extras"
+
+if has tests; then
+  timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
+  timeout 1200 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -6 gpurun_out/pytest_gpu.log
+fi
+if has bench; then
+  timeout 300 python bench.py --impl reference --steps 30 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "bench ref rc=$?"
+  timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
+fi
+if has ncu; then
+  $BENCH_SMALL > gpurun_out/plain.log 2>&1 &&
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $BENCH_SMALL > gpurun_out/ncu_list.log 2>&1
+  echo "ncu list rc=$?"
+  $BENCH_SMALL > gpurun_out/plain2.log 2>&1 &&
+  ncu --set full --clock-control none --import-source on -k "regex:ew_kernel|dot_kernel" -s 20 -c 12 -f -o gpurun_out/prof_timed $BENCH_SMALL > gpurun_out/ncu_full.log 2>&1
+  echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log
+fi
+if has sweep; then
+  timeout 900 python tools/sweep.py --kernels triad,copy,mul,add,nstream,dot,init --log2n 29,25 --dtype f64 --out gpurun_out/sweep_f64.csv > gpurun_out/sweep_f64.log 2>&1; echo "sweep f64 rc=$?"
+  timeout 600 python tools/sweep.py --quick --kernels triad,copy,mul,add,nstream,dot --log2n 30,26 --dtype f32 --out gpurun_out/sweep_f32.csv > gpurun_out/sweep_f32.log 2>&1; echo "sweep f32 rc=$?"
+  timeout 300 python tools/sweep.py --kernels copy_async --log2n 29,25 --out gpurun_out/sweep_copy_async.csv > gpurun_out/sweep_copy_async.log 2>&1
+  timeout 200 python tools/sweep.py --pad-test 29 --out gpurun_out/pad_test.csv > gpurun_out/pad_test.log 2>&1; echo "pad rc=$?"
+fi
+if has sweep2; then
+  timeout 600 python tools/sweep.py --quick --kernels triad,add,copy,mul,nstream,init --log2n 29,25 --dtype f64 --out gpurun_out/sweep2_f64.csv > gpurun_out/sweep2_f64.log 2>&1; echo "sweep2 rc=$?"
+  timeout 300 python tools/sweep.py --quick --kernels triad,copy,dot,nstream --log2n 20,22,23 --dtype f64 --out gpurun_out/sweep2_small.csv > gpurun_out/sweep2_small.log 2>&1
+  grep -A4 "==" gpurun_out/sweep2_f64.log | head -80; grep -A3 "==" gpurun_out/sweep2_small.log | head -60
+fi
+if has sizes; then
+  timeout 1500 python tools/size_sweep.py --out gpurun_out/size_sweep.csv > gpurun_out/size_sweep.log 2>&1; echo "sizes rc=$?"; cat gpurun_out/size_sweep.log
+fi
+if has driver; then
+  for s in 33554432 536870912; do
+    for rep in 1 2; do
+      timeout 200 ./oracle/_ref/cuda-stream --csv --gigabytes -s $s --only All > gpurun_out/drv_ref_cuda_${s}_$rep.csv 2>&1
+      timeout 200 ./build/b200-stream --csv --gigabytes -s $s --only All > gpurun_out/drv_b200_${s}_$rep.csv 2>&1
+    done
+    BABELSTREAM_B200_SYNC=spin timeout 200 ./build/b200-stream --csv --gigabytes -s $s --only All > gpurun_out/drv_b200_spin_${s}.csv 2>&1
+  done
+  timeout 200 ./oracle/_ref/cuda-stream --csv --gigabytes -s 67108864 --float > gpurun_out/drv_ref_cuda_f32.csv 2>&1
+  timeout 200 ./build/b200-stream --csv --gigabytes -s 67108864 --float > gpurun_out/drv_b200_f32.csv 2>&1
+  grep -H -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," gpurun_out/drv_*.csv | cut -d, -f1,5,6
+fi
+echo "gpu_round done"

@@ -47,29 +47,53 @@ def configs(kernel, quick):
             for hint in ((1, 3) if variant == "bulk" else (1,)):
                 yield dict(variant=variant, stages=stages, chunk_bytes=chunk, grid=grid, cache_hint=hint)
         return
-    vec_unroll = [(16, 1), (16, 2), (16, 4), (16, 8), (32, 1), (32, 2), (32, 4)]
+    vec_unroll = [(8, 1), (8, 2), (8, 4), (16, 1), (16, 2), (16, 4), (16, 8), (32, 1), (32, 2), (32, 4)]
     hints = (1, 2, 3, 4, 5)
     if kernel == "dot":
         blocks = (256, 512, 1024)
         grids = (-1, -2, -4, -8)
         variants = ("ticket", "two_pass")
     else:
-        blocks = (128, 256, 512)
-        grids = (2 ** 31 - 1, -2, -4, -8, -16, -32)
+        blocks = (128, 256, 512, 1024)
+        grids = (2 ** 31 - 1, -4) if not quick else (2 ** 31 - 1,)
         variants = ("ldst",)
     if quick:
-        hints = (1, 2, 3)
-        blocks = blocks[1:2]
+        hints = (1, 3)
+        blocks = (256, 512, 1024) if kernel != "dot" else (256, 512)
     for (v, u), b, g, h, var in itertools.product(vec_unroll, blocks, grids, hints, variants):
         if kernel == "dot" and b == 1024 and v * u >= 128:
             continue
         if kernel != "dot" and (b * (-g if g < 0 else 1) > 2048 and g < 0):
             continue  # more threads per SM than can be resident: pointless for a persistent grid
+        if kernel != "dot" and b == 1024 and v * u > 32:
+            continue
         yield dict(vec_bytes=v, unroll=u, block=b, grid=g, cache_hint=h, variant=var)
+
+
+def pad_test(log2n, out_path):
+    """Do the three streams collide in DRAM banks/channels when a, b, c are laid out at identical offsets modulo
+    large powers of two?  Time triad with b and c displaced by a pad inside one big allocation."""
+    n, eb = 1 << log2n, 8
+    st = torch.cuda.current_stream().cuda_stream
+    rows = []
+    big = torch.zeros(3 * n + 3 * (1 << 22), dtype=torch.float64, device="cuda")
+    for pad in (0, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096, 8192, 1 << 14, 1 << 16, 1 << 17, 1 << 18, 1 << 20, 3 << 18):
+        a = big[0:n]
+        b = big[n + pad: 2 * n + pad]
+        c = big[2 * n + 2 * pad: 3 * n + 2 * pad]
+        for name, kw in (("v32u2", dict(vec_bytes=32, unroll=2)), ("v16u8", dict(vec_bytes=16, unroll=8))):
+            cfg = bs.LaunchCfg.make(block=256, cache_hint=2, **kw)
+            ms = time_launch(lambda: bs.launch("triad", a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, cfg=cfg, stream=st), 20)
+            rows.append(dict(pad_elems=pad, pad_bytes=pad * 8, cfg=name, ms=round(ms, 6), gbs=round(3 * n * eb / ms / 1e6, 1)))
+            print(rows[-1])
+    with open(out_path, "w", newline="") as f:
+        w = csv.DictWriter(f, fieldnames=list(rows[0].keys()))
+        w.writeheader(); w.writerows(rows)
 
 
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--pad-test", type=int, default=0, help="log2 n for the array-displacement experiment")
     ap.add_argument("--kernels", default="triad,copy,add,mul,nstream,dot,copy_async")
     ap.add_argument("--log2n", default="25,29")
     ap.add_argument("--dtype", default="f64")
@@ -78,6 +102,9 @@ def main():
     ap.add_argument("--budget-s", type=float, default=1e9)
     args = ap.parse_args()
 
+    if args.pad_test:
+        pad_test(args.pad_test, args.out)
+        return
     tdt = torch.float64 if args.dtype == "f64" else torch.float32
     eb = 8 if args.dtype == "f64" else 4
     st = torch.cuda.current_stream().cuda_stream
