@@ -12,6 +12,7 @@
 #include <nccl.h>  // types only: the library is dlopen'ed, so single-GPU use needs no NCCL at all
 
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <mutex>
 #include <new>
@@ -118,6 +119,12 @@ struct b200_ctx {
   void* host[3] = {nullptr, nullptr, nullptr};
   bool host_pinned = false;
 
+  // opt-in host-side profile of the blocking path (BABELSTREAM_B200_HOSTPROF=1): ns spent in
+  // cudaSetDevice / enqueue / wait, printed by b200_destroy
+  bool hostprof = false;
+  uint64_t prof_ns[3] = {0, 0, 0};
+  uint64_t prof_calls = 0;
+
   // workers (ngpus > 1)
   std::vector<std::thread> workers;
   Command cmd;
@@ -176,11 +183,16 @@ static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd) {
 static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
   Shard* s = ctx->shards[g];
   const size_t eb = (size_t)ctx->elem_bytes;
+  using clk = std::chrono::steady_clock;
+  clk::time_point t0, t1, t2;
+  if (ctx->hostprof) t0 = clk::now();
   // G == 1 runs on the caller's thread, whose current device may have been changed since create
   if (ctx->ngpus == 1) B200_CUDA(cudaSetDevice(s->dev));
   if (cmd.kind == CMD_KERNEL) {
+    if (ctx->hostprof) t1 = clk::now();
     if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev0, s->stream));
     if (int rc = shard_launch(ctx, s, cmd)) return rc;
+    if (ctx->hostprof) t2 = clk::now();
     if (cmd.kernel == B200_DOT && ctx->ngpus > 1 && ctx->combine == COMBINE_NCCL) {
       // the one collective of the whole benchmark: G partial sums -> every GPU holds the total
       char* buf = static_cast<char*>(s->dot_dev);
@@ -190,6 +202,13 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
     }
     if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev1, s->stream));
     if (int rc = stream_wait(ctx, s)) return rc;
+    if (ctx->hostprof && g == 0) {
+      const clk::time_point t3 = clk::now();
+      ctx->prof_ns[0] += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count();
+      ctx->prof_ns[1] += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(t2 - t1).count();
+      ctx->prof_ns[2] += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(t3 - t2).count();
+      ctx->prof_calls++;
+    }
     if (ctx->timing) B200_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
     return B200_OK;
   }
@@ -357,6 +376,10 @@ extern "C" {
 
 void b200_destroy(b200_ctx* ctx) {
   if (!ctx) return;
+  if (ctx->hostprof && ctx->prof_calls)
+    fprintf(stderr, "b200 hostprof: %llu calls; per call: set_device %.0f ns, enqueue %.0f ns, wait %.0f ns\n",
+            (unsigned long long)ctx->prof_calls, (double)ctx->prof_ns[0] / ctx->prof_calls,
+            (double)ctx->prof_ns[1] / ctx->prof_calls, (double)ctx->prof_ns[2] / ctx->prof_calls);
   if (!ctx->workers.empty()) {
     Command q; q.kind = CMD_QUIT;
     ctx->cmd = q;
@@ -415,6 +438,8 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
     for (const char* p = k; *p; p++) env += (char)toupper(*p);
     if (const char* v = getenv(env.c_str())) { rc = apply_option(ctx, k, v); if (rc) return fail(rc); }
   }
+
+  if (const char* hp = getenv("BABELSTREAM_B200_HOSTPROF")) ctx->hostprof = atoi(hp) != 0;
 
   for (int g = 0; g < ngpus; g++) {
     Shard* s = new (std::nothrow) Shard;

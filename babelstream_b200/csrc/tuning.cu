@@ -73,12 +73,14 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
     case B200_NSTREAM: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
     case B200_INIT: r.vec_bytes = 32; r.unroll = 1; r.block = 256; break;
     case B200_DOT:
-      // read-only: a bounded grid-stride grid (the partials must fit the workspace).  Large inputs
-      // want long tiles on 8 blocks per SM (7.44 TB/s at 2^29); mid sizes a short 2-per-SM grid
-      // whose tail is cheap (6.77 TB/s at 2^25).
+      // read-only: a bounded grid-stride grid (the partials must fit the workspace).  Tuned in the
+      // driver's own situation -- blocking call, issued right after triad whose dirty lines are
+      // still draining from L2 (profiles/r01/sweep_dot_blocking_after_triad.csv): 8 blocks of 512
+      // threads per SM (two waves, the second balancing the first) with 2 x 16-byte loads per
+      // operand in flight is within 1.1 % of the best shape at 2^25, 2^27 and 2^29; shapes with
+      // less than full occupancy win in isolation but lose up to 10 % in sequence.
       r.variant = B200_VARIANT_DOT_TICKET;
-      if (bytes_moved >= 2.0 * 1024 * 1024 * 1024) { r.vec_bytes = 32; r.unroll = 4; r.block = 512; r.grid_policy = -8; }
-      else { r.vec_bytes = 16; r.unroll = 8; r.block = 256; r.grid_policy = -2; }
+      r.vec_bytes = 16; r.unroll = 2; r.block = 512; r.grid_policy = -8;
       r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
       break;
   }

@@ -30,10 +30,11 @@ macro(setup)
         cmake_policy(SET CMP0104 OLD)
     endif ()
     set(CMAKE_CXX_STANDARD 14)
+    set(CMAKE_CUDA_STANDARD 17)
     enable_language(CUDA)
     # sm_100a only; -fmad=false because every FMA is written by hand (rounding parity with omp/serial)
     set(CMAKE_CUDA_FLAGS ${CMAKE_CUDA_FLAGS} "-forward-unknown-to-host-compiler"
-            "-gencode arch=compute_100a,code=sm_100a" "-lineinfo" "-fmad=false" "-std=c++17" ${CUDA_EXTRA_FLAGS})
+            "-gencode arch=compute_100a,code=sm_100a" "-lineinfo" "-fmad=false" ${CUDA_EXTRA_FLAGS})
     string(REPLACE ";" " " CMAKE_CUDA_FLAGS "${CMAKE_CUDA_FLAGS}")
     wipe_gcc_style_optimisation_flags(CMAKE_CUDA_FLAGS_${BUILD_TYPE})
     include_directories(${B200_INCLUDE_DIR})

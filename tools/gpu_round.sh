@@ -37,6 +37,27 @@ fi
 if has sizes; then
   timeout 1500 python tools/size_sweep.py --out gpurun_out/size_sweep.csv > gpurun_out/size_sweep.log 2>&1; echo "sizes rc=$?"; cat gpurun_out/size_sweep.log
 fi
+if has block; then
+  timeout 600 python tools/sweep.py --blocking --quick --kernels dot,triad,add,copy,mul,nstream --log2n 25,23 --dtype f64 --out gpurun_out/sweep_blocking.csv > gpurun_out/sweep_blocking.log 2>&1; echo "blocking sweep rc=$?"
+  grep -A5 "==" gpurun_out/sweep_blocking.log | head -120
+  timeout 300 python tools/sweep.py --blocking --kernels dot --log2n 25,27 --dtype f64 --out gpurun_out/sweep_blocking_dot.csv > gpurun_out/sweep_blocking_dot.log 2>&1
+  grep -A8 "==" gpurun_out/sweep_blocking_dot.log | head -40
+fi
+if has small; then
+  timeout 500 python tools/sweep.py --blocking --quick --kernels copy,mul,add,triad,nstream,dot,init --log2n 20,21,22 --dtype f64 --out gpurun_out/sweep_blocking_small.csv > gpurun_out/sweep_blocking_small.log 2>&1; echo "small rc=$?"
+  grep -A4 "==" gpurun_out/sweep_blocking_small.log | head -150
+fi
+if has dotseq; then
+  timeout 400 python tools/sweep.py --blocking --after triad --kernels dot --log2n 25,27,29 --dtype f64 --out gpurun_out/sweep_dot_after_triad.csv > gpurun_out/sweep_dot_after_triad.log 2>&1
+  grep -A10 "==" gpurun_out/sweep_dot_after_triad.log | head -40
+fi
+if has overhead; then
+  for i in 1 2; do
+    ./oracle/_ref/cuda-stream --csv -s 1024 -n 3000 2>&1 | grep -E "^(Copy|Triad|Dot)," | cut -d, -f1,6,8
+    BABELSTREAM_B200_HOSTPROF=1 ./build/b200-stream --csv -s 1024 -n 3000 2>&1 | grep -E "^(Copy|Triad|Dot),|hostprof" | cut -d, -f1,6,8
+    BABELSTREAM_B200_SYNC=spin BABELSTREAM_B200_HOSTPROF=1 ./build/b200-stream --csv -s 1024 -n 3000 2>&1 | grep -E "^(Copy|Triad|Dot),|hostprof" | cut -d, -f1,6,8
+  done
+fi
 if has driver; then
   for s in 33554432 536870912; do
     for rep in 1 2; do

@@ -38,6 +38,26 @@ def time_launch(fn, reps, warm=3):
     return e0.elapsed_time(e1) / reps  # ms
 
 
+def time_blocking(fn, reps, warm=3, before=None):
+    """The driver's way (src/main.cpp:109-116,154-165): host clock around launch + wait, best of reps.
+    `before` (untimed, synchronised) runs ahead of every timed call to reproduce the cache state the
+    kernel meets in the driver's sequence, e.g. triad's dirty lines still in L2 when dot starts."""
+    stream = torch.cuda.current_stream()
+    for _ in range(warm):
+        fn()
+    stream.synchronize()
+    best = 1e30
+    for _ in range(reps):
+        if before is not None:
+            before()
+            stream.synchronize()
+        t0 = time.perf_counter()
+        fn()
+        stream.synchronize()
+        best = min(best, time.perf_counter() - t0)
+    return best * 1e3
+
+
 def configs(kernel, quick):
     if kernel == "copy_async":
         for variant, stages, chunk, grid in itertools.product(("bulk", "tma"), (2, 3, 4, 6, 8), (8192, 16384, 32768, 49152, 65536),
@@ -99,7 +119,9 @@ def main():
     ap.add_argument("--dtype", default="f64")
     ap.add_argument("--out", default="gpurun_out/sweep.csv")
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--blocking", action="store_true", help="time launch+wait per call with the host clock (min), like the driver")
     ap.add_argument("--budget-s", type=float, default=1e9)
+    ap.add_argument("--after", default="", help="with --blocking: run this kernel (default config) before every timed call")
     args = ap.parse_args()
 
     if args.pad_test:
@@ -132,12 +154,13 @@ def main():
                 else:
                     fn = lambda: bs.launch(base, a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, cfg=cfg, stream=st)
                 try:
-                    ms = time_launch(fn, reps)
+                    before = (lambda: bs.launch(args.after, a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, stream=st)) if args.after else None
+                    ms = time_blocking(fn, max(reps, 20), before=before) if args.blocking else time_launch(fn, reps)
                 except bs.B200Error as e:
                     print("skip", kernel, kw, e)
                     continue
                 gbs = nbytes / ms / 1e6
-                row = dict(kernel=kernel, dtype=args.dtype, log2n=log2n, ms=round(ms, 6), gbs=round(gbs, 1), reps=reps,
+                row = dict(kernel=kernel, dtype=args.dtype, log2n=log2n, mode="blocking" if args.blocking else "back_to_back", ms=round(ms, 6), gbs=round(gbs, 1), reps=reps,
                            l2_note="arrays>L2" if 3 * n * eb > 2 * (126 << 20) else "L2-resident", **{k: kw.get(k, "") for k in
                            ("vec_bytes", "unroll", "block", "grid", "cache_hint", "variant", "stages", "chunk_bytes")})
                 rows.append(row)
