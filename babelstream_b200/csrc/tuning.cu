@@ -48,7 +48,7 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   const double footprint = 3.0 * (double)n * elem_bytes;
   const bool l2_resident = footprint <= 0.8 * (double)l2_bytes;
   const double bytes_moved = (double)arrays_touched(kernel) * (double)n * elem_bytes;
-  const bool tiny = bytes_moved < 4.0 * 1024 * 1024;  // latency-bound: favour many small blocks
+  (void)bytes_moved;
 
   Resolved r;
   memset(&r, 0, sizeof r);
@@ -84,7 +84,13 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
       r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
       break;
   }
-  if (tiny && kernel != B200_DOT) { r.block = 256; }  // latency-bound: more, smaller blocks
+  if (l2_resident) {
+    // Working set inside L2 (<= 2^22 doubles): the call is launch-latency bound (8-20 us, of which
+    // ~9 us is launch + wait) and fatter threads in smaller blocks finish sooner; driver-timed
+    // candidates at 2^20..2^22, profiles/r01/small_size_candidates.txt.
+    if (kernel == B200_DOT) { r.vec_bytes = 32; r.unroll = 4; r.block = 256; r.grid_policy = -2; }
+    else { r.vec_bytes = 16; r.unroll = 4; r.block = 128; }
+  }
   r.contract = 1;
   r.stages = 4;
   r.chunk_bytes = 32768;

@@ -95,7 +95,7 @@ def test_resolve_cfg_defaults_and_overrides():
                                                                       cache_hint="stream", variant="bulk", contract="off"))
     assert (o.vec_bytes, o.unroll, o.block, o.grid, o.cache_hint, o.variant, o.contract) == (16, 8, 128, -3, 4, 2, 2)
     assert grid == 3 * 148
-    _, grid = bs.resolve_cfg("add", 1000, 8, num_sms=148, cfg=bs.LaunchCfg.make(grid=-8))
+    _, grid = bs.resolve_cfg("add", 1000, 8, num_sms=148, cfg=bs.LaunchCfg.make(grid=-8, unroll=1, block=256))
     assert grid == 2, "never more blocks than tiles (500 16-byte vectors / 256 threads = 2 tiles)"
     scalar, _ = bs.resolve_cfg("mul", 1000, 4, cfg=bs.LaunchCfg.make(vec_bytes=4))
     assert scalar.unroll == 4 and scalar.cache_hint == 1, "the float scalar path has one compiled shape"

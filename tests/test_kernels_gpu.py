@@ -134,6 +134,31 @@ def test_copy_async_variants_bit_exact(variant, dtype):
     assert same_bits(gc, a0)
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_ieee_edge_cases_match_cpu(orc, dtype):
+    """Denormals (no flush-to-zero), signed zeros, infinities, overflow and NaN: the GPU result must
+    carry the same bits as the CPU reference wherever that is a number, and be NaN wherever that is NaN
+    (NaN payloads are the one thing x86 and NVIDIA hardware legitimately differ in)."""
+    fi = np.finfo(dtype)
+    tiny, big = fi.tiny, fi.max
+    specials = np.array([0.0, -0.0, tiny, -tiny, tiny / 4, -tiny / 8, fi.smallest_subnormal, big, -big, big / 2,
+                         np.inf, -np.inf, np.nan, 1.0, -1.0, 0.4, 2.5, 1e-30 if dtype is np.float32 else 1e-300],
+                        dtype=dtype)
+    grid = np.array(np.meshgrid(specials, specials, specials)).reshape(3, -1)
+    a0, b0, c0 = (np.ascontiguousarray(grid[i]).astype(dtype) for i in range(3))
+    u = np.uint32 if dtype is np.float32 else np.uint64
+    for kern in EW:
+        for contract in (True, False):
+            a, b, c = a0.copy(), b0.copy(), c0.copy()
+            with np.errstate(all="ignore"):
+                oracle_apply(orc, kern, a, b, c, contract)
+            ga, gb, gc = gpu_apply(kern, a0, b0, c0, cfg=bs.LaunchCfg.make(contract=contract))
+            for want, got in ((a, ga), (b, gb), (c, gc)):
+                nan = np.isnan(want)
+                assert np.array_equal(np.isnan(got), nan), (kern, contract)
+                assert np.array_equal(got.view(u)[~nan], want.view(u)[~nan]), (kern, contract)
+
+
 def gpu_dot(a0, b0, cfg=None, repeats=1):
     n, dt = a0.size, a0.dtype
     a = torch.from_numpy(a0).cuda()

@@ -3,11 +3,12 @@
 # BASELINE configs 4 and 5.   Usage: bash tools/gpu_multi.sh N [big]
 set -u
 N=${1:-2}
+START_G=${START_G:-1}
 mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/multi_smi_$N.txt
 nvidia-smi topo -m >> gpurun_out/multi_smi_$N.txt 2>&1
 timeout 900 python -m pytest tests -m gpu -q -k "multi_gpu or driver_multi" > gpurun_out/pytest_multi_$N.log 2>&1; echo "pytest multi rc=$?"; tail -5 gpurun_out/pytest_multi_$N.log
-G=1
+G=$START_G
 while [ $G -le $N ]; do
   if [ $G -eq 1 ]; then
     timeout 600 python bench.py --gpus 1 --steps 100 --warmup 5 --no-extras > gpurun_out/scale_$G.json 2> gpurun_out/scale_$G.err
@@ -23,7 +24,7 @@ except Exception as e: print('parse failed',e); print(open('gpurun_out/scale_$G.
   G=$((G*2))
 done
 # BASELINE config 4: --only Triad / Nstream at 2^30 fp64, G = 1, 2, 4, 8 (strong scaling through the unmodified driver)
-G=1
+G=$START_G
 while [ $G -le $N ]; do
   for K in Triad Nstream; do
     BABELSTREAM_B200_NGPUS=$G timeout 600 ./build/b200-stream --csv --gigabytes -s 1073741824 -n 30 --only $K 2> gpurun_out/cfg4_${K}_$G.err | grep -E "^(Triad|Nstream)," | sed "s/^/G=$G /"

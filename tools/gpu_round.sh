@@ -43,6 +43,14 @@ if has block; then
   timeout 300 python tools/sweep.py --blocking --kernels dot --log2n 25,27 --dtype f64 --out gpurun_out/sweep_blocking_dot.csv > gpurun_out/sweep_blocking_dot.log 2>&1
   grep -A8 "==" gpurun_out/sweep_blocking_dot.log | head -40
 fi
+if has smallcfg; then
+  for s in 1048576 2097152 4194304; do
+    ./oracle/_ref/cuda-stream --csv --gigabytes -s $s --only All -n 20 2>/dev/null | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,5 | tr '\n' ' ' | sed "s/^/s=$s ref_cuda: /"; echo
+    for cfg in "" "all:vec=8,unroll=4,block=256" "all:vec=16,unroll=2,block=256" "all:vec=16,unroll=1,block=256" "all:vec=32,unroll=1,block=256" "all:vec=16,unroll=4,block=256" "all:vec=32,unroll=2,block=256" "all:vec=16,unroll=4,block=128" "all:vec=16,unroll=2,block=128;dot:block=256,grid=-4,unroll=4" "dot:block=256,grid=-2,unroll=4,vec=32" "dot:block=512,grid=-1,unroll=2,vec=32" "dot:block=256,grid=-8,unroll=4,vec=32"; do
+      BABELSTREAM_B200_TUNE="$cfg" ./build/b200-stream --csv --gigabytes -s $s --only All -n 20 2>/dev/null | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,5 | tr '\n' ' ' | sed "s/^/s=$s [$cfg]: /"; echo
+    done
+  done
+fi
 if has small; then
   timeout 500 python tools/sweep.py --blocking --quick --kernels copy,mul,add,triad,nstream,dot,init --log2n 20,21,22 --dtype f64 --out gpurun_out/sweep_blocking_small.csv > gpurun_out/sweep_blocking_small.log 2>&1; echo "small rc=$?"
   grep -A4 "==" gpurun_out/sweep_blocking_small.log | head -150
