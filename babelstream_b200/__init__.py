@@ -20,6 +20,7 @@ from .stream import (  # noqa: F401
     lib_path,
     launch,
     launch_dot,
+    launch_dot_allreduce_p2p,
     dot_workspace_bytes,
     device_count,
     launch_count,
@@ -27,6 +28,6 @@ from .stream import (  # noqa: F401
     shard_range,
 )
 
-__all__ = ["B200Error", "B200Stream", "LaunchCfg", "lib", "lib_path", "launch", "launch_dot",
+__all__ = ["B200Error", "B200Stream", "LaunchCfg", "lib", "lib_path", "launch", "launch_dot", "launch_dot_allreduce_p2p",
            "dot_workspace_bytes", "device_count", "launch_count", "resolve_cfg", "shard_range",
            "KERNELS", "KERNEL_IDS", "WEIGHTS", "HINTS", "VARIANTS"]

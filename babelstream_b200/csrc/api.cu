@@ -178,8 +178,9 @@ int b200_launch_nstream(void* a, const void* b, const void* c, size_t n, int ele
 
 size_t b200_dot_workspace_bytes(void) { return kDotWorkspaceBytes; }
 
-int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
-                    void* result_host_mapped, const b200_launch_cfg* cfg, void* stream) {
+static int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                             void* result_host_mapped, int world, int rank, unsigned long long seq,
+                             void* const* mailboxes, const b200_launch_cfg* cfg, void* stream) {
   if (int rc = check_common(n, elem_bytes)) return rc;
   if (!workspace || (n > 0 && (!a || !b))) { set_error("b200_launch_dot: null pointer"); return B200_EINVAL; }
   const DeviceProps* props = current_device_props(nullptr);
@@ -188,10 +189,27 @@ int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void
   if (int rc = resolve_cfg(B200_DOT, n, elem_bytes, props->num_sms, props->l2_bytes, cfg, &call.r)) return rc;
   call.a = a; call.b = b; call.n = n; call.elem_bytes = elem_bytes;
   call.workspace = workspace; call.result_dev = result_dev; call.result_host = result_host_mapped;
+  call.p2p_world = world; call.p2p_rank = rank; call.p2p_seq = seq; call.p2p_mailboxes = mailboxes;
   call.stream = static_cast<cudaStream_t>(stream);
   call.g = make_geometry(a, b, nullptr, n, elem_bytes, call.r.vec_bytes, call.r.block, call.r.unroll, call.r.cache_hint);
   call.grid = grid_for(call.r.grid_policy, call.g.ntiles, props->num_sms);
   return launch_dot_impl(call);
+}
+
+int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                    void* result_host_mapped, const b200_launch_cfg* cfg, void* stream) {
+  return launch_dot_common(a, b, n, elem_bytes, workspace, result_dev, result_host_mapped, 0, 0, 0, nullptr, cfg, stream);
+}
+
+size_t b200_dot_mailbox_bytes(void) { return sizeof(MailSlot) * kMaxPeers; }
+
+int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int elem_bytes, void* workspace,
+                                  void* result_dev, void* result_host_mapped, int world, int rank,
+                                  unsigned long long seq, void* const* mailboxes, const b200_launch_cfg* cfg,
+                                  void* stream) {
+  if (world < 1 || world > kMaxPeers) { set_error("dot p2p: world must be 1..%d", kMaxPeers); return B200_EINVAL; }
+  return launch_dot_common(a, b, n, elem_bytes, workspace, result_dev, result_host_mapped, world, rank, seq, mailboxes,
+                           cfg, stream);
 }
 
 }  // extern "C"

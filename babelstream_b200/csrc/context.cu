@@ -70,7 +70,7 @@ struct NcclApi {
 };
 
 enum { CMD_NONE = 0, CMD_KERNEL, CMD_READ, CMD_WRITE, CMD_QUIT };
-enum { COMBINE_NCCL = 0, COMBINE_HOST = 1 };
+enum { COMBINE_NCCL = 0, COMBINE_HOST = 1, COMBINE_P2P = 2 };
 enum { SYNC_STREAM = 0, SYNC_SPIN = 1 };
 
 struct Shard {
@@ -82,6 +82,8 @@ struct Shard {
   void* dot_dev = nullptr;       // 2 x 8 bytes: [0] this GPU's partial, [1] all-reduced value
   void* dot_host = nullptr;      // mapped pinned, 8 bytes
   void* dot_host_dev = nullptr;  // device-side alias of dot_host
+  void* mailbox = nullptr;       // p2p combine: kMaxPeers slots in this GPU's HBM, written by the peers
+  int rank = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   ncclComm_t comm = nullptr;
   float last_ms = -1.f;
@@ -94,6 +96,7 @@ struct Command {
   int kind = CMD_NONE;
   int kernel = 0;
   double s0 = 0, s1 = 0, s2 = 0;
+  unsigned long long seq = 0;                   // dot: sequence number of the p2p all-reduce
   void* host[3] = {nullptr, nullptr, nullptr};  // read: destinations; write: sources
 };
 
@@ -114,6 +117,9 @@ struct b200_ctx {
   int combine = COMBINE_NCCL;
   NcclApi nccl;
   bool nccl_ready = false;
+  bool p2p_ready = false;
+  void* mailboxes[kMaxPeers] = {};
+  unsigned long long dot_seq = 0;
 
   // host mirrors for get_arrays
   void* host[3] = {nullptr, nullptr, nullptr};
@@ -156,6 +162,11 @@ static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd) {
   void* st = s->stream;
   if (cmd.kernel == B200_DOT) {
     const bool single = ctx->ngpus == 1;
+    if (!single && ctx->combine == COMBINE_P2P) {
+      // fused: partial + all-reduce over peer memory in ONE launch; an empty shard still takes part
+      return b200_launch_dot_allreduce_p2p(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, s->dot_host_dev, ctx->ngpus,
+                                           s->rank, cmd.seq, ctx->mailboxes, cfg, st);
+    }
     // single GPU: the kernel writes the sum straight into mapped host memory (zero-copy)
     if (s->count == 0) {
       B200_CUDA(cudaMemsetAsync(s->dot_dev, 0, 8, s->stream));
@@ -306,7 +317,7 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
   } else if (key == "dot_variant") {
     ctx->tune[B200_DOT].variant = val == "two_pass" ? B200_VARIANT_DOT_TWO_PASS : val == "ticket" ? B200_VARIANT_DOT_TICKET : 0;
   } else if (key == "dot_combine") {
-    ctx->combine = val == "host" ? COMBINE_HOST : COMBINE_NCCL;
+    ctx->combine = val == "host" ? COMBINE_HOST : val == "p2p" ? COMBINE_P2P : COMBINE_NCCL;
   } else if (key == "timing") {
     ctx->timing = (val == "1" || val == "on" || val == "true");
   } else if (key == "sync") {
@@ -369,6 +380,47 @@ static int ensure_host_mirrors(b200_ctx* ctx) {
   return B200_OK;
 }
 
+// Bring up whatever the selected multi-GPU dot combine needs.  Caller's thread, workers idle.
+static int ensure_combine_ready(b200_ctx* ctx) {
+  if (ctx->ngpus == 1 || ctx->combine == COMBINE_HOST) return B200_OK;
+  if (ctx->combine == COMBINE_NCCL) {
+    if (ctx->nccl_ready) return B200_OK;
+    if (int rc = ctx->nccl.load()) return rc;
+    std::vector<int> devs(ctx->ngpus);
+    std::vector<ncclComm_t> comms(ctx->ngpus);
+    for (int g = 0; g < ctx->ngpus; g++) devs[g] = ctx->first_device + g;
+    ncclResult_t r = ctx->nccl.CommInitAll(comms.data(), ctx->ngpus, devs.data());
+    if (r != ncclSuccess) { set_error("ncclCommInitAll failed: %s", ctx->nccl.GetErrorString(r)); return B200_ENCCL; }
+    for (int g = 0; g < ctx->ngpus; g++) ctx->shards[g]->comm = comms[g];
+    ctx->nccl_ready = true;
+    cudaSetDevice(ctx->first_device);
+    return B200_OK;
+  }
+  if (ctx->p2p_ready) return B200_OK;
+  if (ctx->ngpus > kMaxPeers) { set_error("dot_combine=p2p supports at most %d GPUs", kMaxPeers); return B200_EUNSUPPORTED; }
+  for (Shard* s : ctx->shards) {
+    B200_CUDA(cudaSetDevice(s->dev));
+    for (Shard* peer : ctx->shards) {
+      if (peer == s) continue;
+      int can = 0;
+      B200_CUDA(cudaDeviceCanAccessPeer(&can, s->dev, peer->dev));
+      if (!can) { set_error("GPU %d cannot access GPU %d: dot_combine=p2p needs NVLink/PCIe peer access", s->dev, peer->dev); return B200_EUNSUPPORTED; }
+      cudaError_t e = cudaDeviceEnablePeerAccess(peer->dev, 0);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+      else if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
+    }
+    if (!s->mailbox) {
+      B200_CUDA(cudaMalloc(&s->mailbox, b200_dot_mailbox_bytes()));
+      B200_CUDA(cudaMemset(s->mailbox, 0, b200_dot_mailbox_bytes()));
+    }
+    ctx->mailboxes[s->rank] = s->mailbox;
+  }
+  for (Shard* s : ctx->shards) { B200_CUDA(cudaSetDevice(s->dev)); B200_CUDA(cudaDeviceSynchronize()); }
+  cudaSetDevice(ctx->first_device);
+  ctx->p2p_ready = true;
+  return B200_OK;
+}
+
 }  // namespace b200
 
 // ---------------------------------------------------------------------------------------------
@@ -395,7 +447,7 @@ void b200_destroy(b200_ctx* ctx) {
     if (s->stream) cudaStreamDestroy(s->stream);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
-    cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); cudaFree(s->dot_ws); cudaFree(s->dot_dev);
+    cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox);
     if (s->dot_host) cudaFreeHost(s->dot_host);
     delete s;
   }
@@ -446,6 +498,7 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
     if (!s) { set_error("out of host memory"); return fail(B200_ENOMEM); }
     ctx->shards.push_back(s);
     s->dev = first_device + g;
+    s->rank = g;
     b200_shard_range(n, elem_bytes, ngpus, g, &s->begin, &s->count);
     auto cu = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && rc == B200_OK) rc = cuda_fail(e, what, __FILE__, __LINE__); };
     cu(cudaSetDevice(s->dev), "cudaSetDevice");
@@ -481,16 +534,8 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
   }
 
   if (ngpus > 1) {
-    if (ctx->combine == COMBINE_NCCL) {
-      if ((rc = ctx->nccl.load())) return fail(rc);
-      std::vector<int> devs(ngpus);
-      std::vector<ncclComm_t> comms(ngpus);
-      for (int g = 0; g < ngpus; g++) devs[g] = first_device + g;
-      ncclResult_t r = ctx->nccl.CommInitAll(comms.data(), ngpus, devs.data());
-      if (r != ncclSuccess) { set_error("ncclCommInitAll failed: %s", ctx->nccl.GetErrorString(r)); return fail(B200_ENCCL); }
-      for (int g = 0; g < ngpus; g++) ctx->shards[g]->comm = comms[g];
-      ctx->nccl_ready = true;
-    }
+    rc = ensure_combine_ready(ctx);
+    if (rc) return fail(rc);
     for (int g = 0; g < ngpus; g++) ctx->workers.emplace_back(worker_main, ctx, g);
   }
   cudaSetDevice(first_device);
@@ -500,11 +545,8 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
 
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value) {
   if (!ctx || !key || !value) { set_error("b200_set_option: null argument"); return B200_EINVAL; }
-  if (std::string(key) == "dot_combine" && ctx->ngpus > 1 && std::string(value) != "host" && !ctx->nccl_ready) {
-    set_error("dot_combine=nccl must be chosen before b200_create (BABELSTREAM_B200_DOT_COMBINE)");
-    return B200_EINVAL;
-  }
-  return apply_option(ctx, key, value);
+  if (int rc = apply_option(ctx, key, value)) return rc;
+  return ensure_combine_ready(ctx);  // e.g. dot_combine switched to nccl or p2p: bring it up now
 }
 
 int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
@@ -529,7 +571,8 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
   if (ctx->ngpus > 1) {
     int v = 0;
     if (ctx->nccl_ready && ctx->nccl.GetVersion) ctx->nccl.GetVersion(&v);
-    snprintf(line, sizeof line, "  dot combine: %s", ctx->combine == COMBINE_NCCL ? "ncclAllReduce(count=1)" : "host sum in rank order");
+    snprintf(line, sizeof line, "  dot combine: %s", ctx->combine == COMBINE_NCCL ? "ncclAllReduce(count=1)"
+             : ctx->combine == COMBINE_P2P ? "fused peer-memory all-reduce inside the dot kernel (NVLink)" : "host sum in rank order");
     out += line;
     if (v) { snprintf(line, sizeof line, " (NCCL %d)", v); out += line; }
     out += "\n";
@@ -542,6 +585,7 @@ static int run_kernel(b200_ctx* ctx, int kernel, double s0, double s1, double s2
   if (!ctx) { set_error("null context"); return B200_EINVAL; }
   Command cmd;
   cmd.kind = CMD_KERNEL; cmd.kernel = kernel; cmd.s0 = s0; cmd.s1 = s1; cmd.s2 = s2;
+  if (kernel == B200_DOT) cmd.seq = ++ctx->dot_seq;
   return run_all(ctx, cmd);
 }
 

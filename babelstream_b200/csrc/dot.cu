@@ -33,6 +33,9 @@ static int launch_dot_typed(const DotCall& call) {
   args.ticket = reinterpret_cast<unsigned int*>(static_cast<char*>(call.workspace) + kDotMaxBlocks * 8);
   args.result_dev = call.result_dev; args.result_host = call.result_host;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
+  args.p2p.world = call.p2p_world; args.p2p.rank = call.p2p_rank; args.p2p.seq = call.p2p_seq;
+  for (int g = 0; g < kMaxPeers; g++)
+    args.p2p.mailbox[g] = (call.p2p_world > 1 && g < call.p2p_world) ? static_cast<MailSlot*>(call.p2p_mailboxes[g]) : nullptr;
   k<<<call.grid, call.r.block, 0, call.stream>>>(args);
   count_launch();
   B200_CUDA(cudaPeekAtLastError());
@@ -50,6 +53,13 @@ static int launch_dot_typed(const DotCall& call) {
 int launch_dot_impl(const DotCall& call) {
   const bool fused = call.r.contract != 2;
   const bool ticket = call.r.variant == B200_VARIANT_DOT_TICKET;
+  if (call.p2p_world > 1) {
+    if (!ticket) { set_error("the fused peer-memory all-reduce needs the ticket variant of dot"); return B200_EINVAL; }
+    if (call.p2p_world > kMaxPeers || call.p2p_rank < 0 || call.p2p_rank >= call.p2p_world || !call.p2p_mailboxes || call.p2p_seq == 0) {
+      set_error("dot p2p: bad world/rank/seq/mailboxes (world %d, rank %d)", call.p2p_world, call.p2p_rank);
+      return B200_EINVAL;
+    }
+  }
   if (call.grid > (unsigned)kDotMaxBlocks) {
     set_error("dot grid %u exceeds the workspace capacity of %d blocks", call.grid, kDotMaxBlocks);
     return B200_EINVAL;

@@ -80,6 +80,10 @@ struct DotCall {
   void* workspace;
   void* result_dev;
   void* result_host;
+  // fused all-reduce over peer memory (p2p_world <= 1: none)
+  int p2p_world = 0, p2p_rank = 0;
+  unsigned long long p2p_seq = 0;
+  void* const* p2p_mailboxes = nullptr;
   Resolved r;
   Geometry g;
   unsigned grid;

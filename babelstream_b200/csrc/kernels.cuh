@@ -339,16 +339,88 @@ __device__ __forceinline__ T block_sum(T v, T* scratch) {
   return v;
 }
 
+// valid in thread 0
 template <typename T>
-__device__ __forceinline__ void dot_second_pass(const T* partials, unsigned nparts, T* scratch, T* result_dev,
-                                                T* result_host) {
+__device__ __forceinline__ T dot_second_pass(const T* partials, unsigned nparts, T* scratch) {
   T v = T(0);
   for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) v = add_rn(v, __ldcg(partials + i));
-  v = block_sum(v, scratch);
-  if (threadIdx.x == 0) {
-    if (result_dev) *result_dev = v;
-    if (result_host) *result_host = v;
+  return block_sum(v, scratch);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused dot + all-reduce over NVLink peer memory (no NCCL, no extra launch).
+// Every GPU owns a mailbox of kMaxPeers slots in its own HBM, mapped into all peers.  The last block
+// of GPU r's dot kernel  (1) stores {value, seq} into slot r of EVERY GPU's mailbox with
+// system-scope release semantics (peer stores travel over NVLink / NVSwitch),  (2) waits until all G
+// slots of its OWN mailbox carry this call's sequence number,  (3) adds the G values in rank order.
+// Every GPU ends up with the same bits.  The G kernels run on G different devices at the same
+// time, so the wait cannot deadlock on scheduling; a globaltimer bound turns a missing peer into a
+// NaN result instead of a hang.
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxPeers = 8;
+struct alignas(16) MailSlot {
+  unsigned long long seq;
+  unsigned long long bits;
+};
+
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+struct P2PArgs {
+  MailSlot* mailbox[kMaxPeers];  // mailbox[g] = GPU g's mailbox as seen from THIS device
+  unsigned long long seq;        // strictly increasing per dot call, equal on all GPUs
+  int world;                     // 0 or 1: no exchange
+  int rank;
+};
+
+template <typename T> __device__ __forceinline__ unsigned long long to_bits(T v);
+template <> __device__ __forceinline__ unsigned long long to_bits<double>(double v) { return (unsigned long long)__double_as_longlong(v); }
+template <> __device__ __forceinline__ unsigned long long to_bits<float>(float v) { return (unsigned long long)__float_as_uint(v); }
+template <typename T> __device__ __forceinline__ T from_bits(unsigned long long b);
+template <> __device__ __forceinline__ double from_bits<double>(unsigned long long b) { return __longlong_as_double((long long)b); }
+template <> __device__ __forceinline__ float from_bits<float>(unsigned long long b) { return __uint_as_float((unsigned)b); }
+
+// Called by warp 0 of the last block; `mine` is this GPU's partial.  Returns the all-reduced sum
+// (identical on every GPU) in every lane.
+template <typename T>
+__device__ __forceinline__ T p2p_allreduce_warp(const P2PArgs& p, T mine) {
+  const int lane = threadIdx.x & 31;
+  bool ok = true;
+  T got = T(0);
+  if (lane < p.world) {
+    MailSlot* dst = p.mailbox[lane] + p.rank;   // my slot in GPU `lane`'s mailbox
+    st_relaxed_sys(&dst->bits, to_bits<T>(mine));
+    st_release_sys(&dst->seq, p.seq);           // value is visible before the sequence number
+    const MailSlot* src = p.mailbox[p.rank] + lane;  // GPU `lane`'s slot in my mailbox (local HBM)
+    const unsigned long long t0 = global_timer_ns();
+    while (ld_acquire_sys(&src->seq) != p.seq) {
+      if (global_timer_ns() - t0 > 2000000000ull) { ok = false; break; }
+    }
+    got = from_bits<T>(ld_relaxed_sys(&src->bits));
   }
+  T total = T(0);
+  for (int r = 0; r < p.world; r++) total = add_rn(total, __shfl_sync(0xffffffffu, got, r));  // rank order
+  if (!__all_sync(0xffffffffu, ok)) total = from_bits<T>(~0ull);  // NaN: a peer never arrived
+  return total;
 }
 
 struct DotArgs {
@@ -360,6 +432,7 @@ struct DotArgs {
   void* result_host;     // mapped pinned, may be null
   unsigned long long nvec, ntiles, n;
   unsigned int head;
+  P2PArgs p2p;           // world <= 1: plain single-GPU dot
 };
 
 // 1024-thread blocks leave 64 registers per thread: not enough for the widest tiles
@@ -444,9 +517,17 @@ dot_kernel(const DotArgs args) {
     }
     __syncthreads();
     if (is_last) {
-      dot_second_pass<T>(partials, gridDim.x, scratch, static_cast<T*>(args.result_dev),
-                         static_cast<T*>(args.result_host));
+      T v = dot_second_pass<T>(partials, gridDim.x, scratch);
       if (threadIdx.x == 0) *args.ticket = 0u;  // ready for the next launch
+      if (args.p2p.world > 1) {                 // fused all-reduce over peer memory (block-uniform branch)
+        if (threadIdx.x == 0) scratch[0] = v;
+        __syncthreads();
+        if (threadIdx.x < 32) v = p2p_allreduce_warp<T>(args.p2p, scratch[0]);
+      }
+      if (threadIdx.x == 0) {
+        if (args.result_dev) *static_cast<T*>(args.result_dev) = v;
+        if (args.result_host) *static_cast<T*>(args.result_host) = v;
+      }
     }
   }
 }
@@ -455,7 +536,11 @@ template <typename T>
 __global__ void __launch_bounds__(1024)
 dot_final_kernel(const T* partials, unsigned nparts, T* result_dev, T* result_host) {
   __shared__ T scratch[32];
-  dot_second_pass<T>(partials, nparts, scratch, result_dev, result_host);
+  const T v = dot_second_pass<T>(partials, nparts, scratch);
+  if (threadIdx.x == 0) {
+    if (result_dev) *result_dev = v;
+    if (result_host) *result_host = v;
+  }
 }
 
 }  // namespace b200

@@ -96,6 +96,8 @@ def lib() -> C.CDLL:
         "b200_launch_nstream": (ci, [vp, vp, vp, sz, ci, d, cfgp, vp]),
         "b200_dot_workspace_bytes": (sz, []),
         "b200_launch_dot": (ci, [vp, vp, sz, ci, vp, vp, vp, cfgp, vp]),
+        "b200_dot_mailbox_bytes": (sz, []),
+        "b200_launch_dot_allreduce_p2p": (ci, [vp, vp, sz, ci, vp, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
         "b200_create": (vp, [ci, ci, sz, ci, C.POINTER(ci)]),
         "b200_destroy": (None, [vp]),
         "b200_set_option": (ci, [vp, cp, cp]),
@@ -194,6 +196,16 @@ def launch_dot(a: int, b: int, n: int, elem_bytes: int, workspace: int, result_d
     """LEVEL 1: enqueue dot; the sum (type T) lands in result_dev.  Asynchronous."""
     _check(lib().b200_launch_dot(a, b, n, elem_bytes, workspace, result_dev or None, result_host_mapped or None,
                                  C.byref(cfg) if cfg is not None else None, C.c_void_p(stream)))
+
+
+def launch_dot_allreduce_p2p(a: int, b: int, n: int, elem_bytes: int, workspace: int, result_dev: int, *, world: int,
+                             rank: int, seq: int, mailboxes, result_host_mapped: int = 0, cfg: LaunchCfg | None = None,
+                             stream: int = 0) -> None:
+    """LEVEL 1: fused dot + all-reduce over peer memory, GPU `rank` of `world` (one call per GPU, each on its device)."""
+    boxes = (C.c_void_p * len(mailboxes))(*mailboxes)
+    _check(lib().b200_launch_dot_allreduce_p2p(a, b, n, elem_bytes, workspace, result_dev or None, result_host_mapped or None,
+                                               world, rank, seq, boxes, C.byref(cfg) if cfg is not None else None,
+                                               C.c_void_p(stream)))
 
 
 class B200Stream:

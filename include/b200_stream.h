@@ -56,12 +56,13 @@ enum { B200_VARIANT_AUTO = 0,
        B200_VARIANT_DOT_TICKET = 2    /* dot: same second pass run by the last block to finish, one launch */ };
 
 /* Launch configuration.  A zeroed struct (or NULL) means "auto": the per-size table in
- * csrc/tuning.cuh.  The reference's counterparts are compile-time: TBSIZE 256, UNROLL_FACTOR 4,
+ * csrc/tuning.cu.  The reference's counterparts are compile-time: TBSIZE 256, UNROLL_FACTOR 4,
  * GRID_STRIDE (src/cuda/CUDAStream.h:18, model.cmake:6-22). */
 typedef struct b200_launch_cfg {
-  int vec_bytes;  /* 0 auto | 4 or 8 = scalar | 16 = 128-bit | 32 = 256-bit accesses */
+  int vec_bytes;  /* 0 auto | 8 = 64-bit | 16 = 128-bit | 32 = 256-bit accesses (4: float scalar path) */
   int unroll;     /* 0 auto | 1,2,4,8 vectors per thread per tile (8 only with 16-byte vectors) */
-  int block;      /* 0 auto | threads per block: 64..512, multiple of 32 (dot: ..1024) */
+  int block;      /* 0 auto | threads per block, multiple of 32: up to 1024 while vec_bytes*unroll <= 32
+                     (dot: < 128), else up to 512 */
   int grid;       /* 0 auto | >0 exact block count (grid-stride) | <0: -k means k blocks per SM |
                      INT32_MAX: one tile per block */
   int cache_hint; /* B200_HINT_* */
@@ -123,6 +124,20 @@ size_t b200_dot_workspace_bytes(void);
 int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
                     void* result_host_mapped, const b200_launch_cfg* cfg, void* stream);
 
+/* Fused dot + all-reduce over NVLink peer memory: ONE launch per GPU, no NCCL.  GPU `rank` of `world`
+ * (<= 8) computes its partial as b200_launch_dot does; the last block then stores it into slot `rank`
+ * of every GPU's mailbox (peer stores), waits for the `world` partials of this call in its own
+ * mailbox and adds them in rank order, so every GPU obtains the same bits.  mailboxes[g] is GPU g's
+ * mailbox (b200_dot_mailbox_bytes() of zero-initialised device memory on GPU g, peer access enabled
+ * from the current device); `seq` must be non-zero, equal on all GPUs and strictly increasing from
+ * call to call.  All `world` launches must be issued (on their own devices) for any to complete;
+ * a peer that never arrives turns the result into NaN after 2 s instead of hanging. */
+size_t b200_dot_mailbox_bytes(void);
+int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int elem_bytes, void* workspace,
+                                  void* result_dev, void* result_host_mapped, int world, int rank,
+                                  unsigned long long seq, void* const* mailboxes, const b200_launch_cfg* cfg,
+                                  void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * LEVEL 2 -- the Stream<T> object: three device-resident arrays of n elements, sharded
  * contiguously over `ngpus` devices first_device .. first_device+ngpus-1, blocking calls
@@ -138,7 +153,8 @@ void b200_destroy(b200_ctx* ctx);
 
 /* "key=value" tuning / behaviour options, also read from the environment at create time as
  * BABELSTREAM_B200_<KEY>.  Keys: contract=fast|off, copy_variant=auto|ldst|bulk|tma,
- * dot_variant=auto|two_pass|ticket, timing=0|1, sync=stream|spin|event,
+ * dot_variant=auto|two_pass|ticket, dot_combine=nccl|p2p|host (multi-GPU dot: one ncclAllReduce |
+ * fused peer-memory all-reduce inside the dot kernel | rank-order sum on the host), timing=0|1, sync=stream|spin,
  * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk) */
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
 int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */

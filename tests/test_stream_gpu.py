@@ -209,7 +209,7 @@ multi = pytest.mark.skipif(bs.lib() is None or bs.device_count() < 2, reason="ne
 
 @multi
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
-@pytest.mark.parametrize("combine", ["nccl", "host"])
+@pytest.mark.parametrize("combine", ["nccl", "host", "p2p"])
 def test_multi_gpu_sharded_bit_exact(orc, dtype, combine):
     os.environ["BABELSTREAM_B200_DOT_COMBINE"] = combine
     try:
@@ -235,8 +235,33 @@ def test_multi_gpu_sharded_bit_exact(orc, dtype, combine):
 
 
 @multi
+def test_dot_combine_modes_agree_and_switch_at_run_time(orc):
+    """nccl, p2p (fused peer-memory all-reduce inside the dot kernel) and host combine the same G partials:
+    p2p and host add them in rank order and must agree bit for bit; nccl within a few ulp."""
+    n, ngpus = (1 << 23) + 5, min(bs.device_count(), 8)
+    rng = np.random.default_rng(1)
+    a0, b0 = np.abs(rng.standard_normal(n)), np.abs(rng.standard_normal(n))
+    with bs.B200Stream(n, dtype=np.float64, ngpus=ngpus, dot_combine="host") as s:
+        s.write_arrays(a0, b0, None)
+        host = s.dot()
+        s.set_option("dot_combine", "p2p")
+        p2p = [s.dot() for _ in range(5)]
+        s.set_option("dot_combine", "nccl")
+        nccl = s.dot()
+        s.set_option("dot_combine", "p2p")
+        again = s.dot()
+        assert "peer-memory" in s.describe()
+    assert all(x.tobytes() == host.tobytes() for x in p2p + [again])
+    exact = float(np.dot(a0, b0))
+    assert abs(float(host) - exact) <= 64 * np.finfo(np.float64).eps * exact
+    assert abs(float(nccl) - float(host)) <= 8 * np.finfo(np.float64).eps * exact
+
+
+@multi
 @needs_bin
 def test_driver_multi_gpu():
-    p = run_bin("-s", str((1 << 24) + 3), "-n", "10", "--only", "All", env={"BABELSTREAM_B200_NGPUS": "2"})
-    assert p.returncode == 0, p.stdout + p.stderr
-    assert "GPUs: 2" in p.stdout
+    for combine in ("nccl", "p2p", "host"):
+        p = run_bin("-s", str((1 << 24) + 3), "-n", "10", "--only", "All",
+                    env={"BABELSTREAM_B200_NGPUS": "2", "BABELSTREAM_B200_DOT_COMBINE": combine})
+        assert p.returncode == 0, p.stdout + p.stderr
+        assert "GPUs: 2" in p.stdout

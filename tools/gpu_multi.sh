@@ -32,7 +32,7 @@ while [ $G -le $N ]; do
   G=$((G*2))
 done
 # all kernels, dot through NCCL vs host combine, at a per-GPU-friendly size
-for COMB in nccl host; do
+for COMB in nccl p2p host; do
   BABELSTREAM_B200_NGPUS=$N BABELSTREAM_B200_DOT_COMBINE=$COMB timeout 600 ./build/b200-stream --csv --gigabytes -s $((33554432*N)) --only All 2> gpurun_out/all_${COMB}_$N.err | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,5,6 | sed "s/^/G=$N $COMB /"
 done
 if [ "${2:-}" = "big" ]; then

@@ -79,3 +79,5 @@ if has driver; then
   grep -H -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," gpurun_out/drv_*.csv | cut -d, -f1,5,6
 fi
 echo "gpu_round done"
+# (compute-sanitizer is closed on this pool: no memcheck/racecheck stages)
+echo "gpu_round end"
