@@ -70,7 +70,7 @@ struct NcclApi {
 };
 
 enum { CMD_NONE = 0, CMD_KERNEL, CMD_READ, CMD_WRITE, CMD_QUIT };
-enum { COMBINE_NCCL = 0, COMBINE_HOST = 1, COMBINE_P2P = 2 };
+enum { COMBINE_AUTO = -1, COMBINE_NCCL = 0, COMBINE_HOST = 1, COMBINE_P2P = 2 };
 enum { SYNC_STREAM = 0, SYNC_SPIN = 1 };
 
 struct Shard {
@@ -114,7 +114,7 @@ struct b200_ctx {
   b200_launch_cfg tune[B200_NUM_KERNELS];
   bool timing = false;
   int sync_mode = SYNC_STREAM;
-  int combine = COMBINE_NCCL;
+  int combine = COMBINE_AUTO;  // resolved by ensure_combine_ready: p2p if every pair has peer access, else nccl
   NcclApi nccl;
   bool nccl_ready = false;
   bool p2p_ready = false;
@@ -317,7 +317,7 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
   } else if (key == "dot_variant") {
     ctx->tune[B200_DOT].variant = val == "two_pass" ? B200_VARIANT_DOT_TWO_PASS : val == "ticket" ? B200_VARIANT_DOT_TICKET : 0;
   } else if (key == "dot_combine") {
-    ctx->combine = val == "host" ? COMBINE_HOST : val == "p2p" ? COMBINE_P2P : COMBINE_NCCL;
+    ctx->combine = val == "host" ? COMBINE_HOST : val == "p2p" ? COMBINE_P2P : val == "nccl" ? COMBINE_NCCL : COMBINE_AUTO;
   } else if (key == "timing") {
     ctx->timing = (val == "1" || val == "on" || val == "true");
   } else if (key == "sync") {
@@ -383,6 +383,18 @@ static int ensure_host_mirrors(b200_ctx* ctx) {
 // Bring up whatever the selected multi-GPU dot combine needs.  Caller's thread, workers idle.
 static int ensure_combine_ready(b200_ctx* ctx) {
   if (ctx->ngpus == 1 || ctx->combine == COMBINE_HOST) return B200_OK;
+  if (ctx->combine == COMBINE_AUTO) {
+    // Default: the fused peer-memory all-reduce (one launch, no NCCL bring-up) whenever every pair of
+    // GPUs has peer access -- always true on an NVSwitch box -- otherwise one ncclAllReduce.
+    bool all_peers = ctx->ngpus <= kMaxPeers;
+    for (Shard* s : ctx->shards)
+      for (Shard* peer : ctx->shards) {
+        int can = 0;
+        if (s != peer && (cudaDeviceCanAccessPeer(&can, s->dev, peer->dev) != cudaSuccess || !can)) all_peers = false;
+      }
+    (void)cudaGetLastError();
+    ctx->combine = all_peers ? COMBINE_P2P : COMBINE_NCCL;
+  }
   if (ctx->combine == COMBINE_NCCL) {
     if (ctx->nccl_ready) return B200_OK;
     if (int rc = ctx->nccl.load()) return rc;

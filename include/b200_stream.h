@@ -153,8 +153,9 @@ void b200_destroy(b200_ctx* ctx);
 
 /* "key=value" tuning / behaviour options, also read from the environment at create time as
  * BABELSTREAM_B200_<KEY>.  Keys: contract=fast|off, copy_variant=auto|ldst|bulk|tma,
- * dot_variant=auto|two_pass|ticket, dot_combine=nccl|p2p|host (multi-GPU dot: one ncclAllReduce |
- * fused peer-memory all-reduce inside the dot kernel | rank-order sum on the host), timing=0|1, sync=stream|spin,
+ * dot_variant=auto|two_pass|ticket, dot_combine=auto|p2p|nccl|host (multi-GPU dot: fused peer-memory
+ * all-reduce inside the dot kernel | one ncclAllReduce | rank-order sum on the host; auto = p2p when
+ * every pair of GPUs has peer access, else nccl), timing=0|1, sync=stream|spin,
  * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk) */
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
 int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */
