@@ -10,7 +10,9 @@ There is no CPU fallback and nothing here imports ``oracle``.
 from .stream import (  # noqa: F401
     B200Error,
     B200Stream,
+    Doorbell,
     LaunchCfg,
+    Mailbox,
     HINTS,
     KERNELS,
     KERNEL_IDS,
@@ -21,6 +23,8 @@ from .stream import (  # noqa: F401
     launch,
     launch_dot,
     launch_dot_allreduce_p2p,
+    launch_doorbell,
+    launch_dot_doorbell,
     dot_workspace_bytes,
     device_count,
     launch_count,
@@ -28,6 +32,7 @@ from .stream import (  # noqa: F401
     shard_range,
 )
 
-__all__ = ["B200Error", "B200Stream", "LaunchCfg", "lib", "lib_path", "launch", "launch_dot", "launch_dot_allreduce_p2p",
+__all__ = ["B200Error", "B200Stream", "LaunchCfg", "Doorbell", "Mailbox", "lib", "lib_path", "launch", "launch_dot",
+           "launch_dot_allreduce_p2p", "launch_doorbell", "launch_dot_doorbell",
            "dot_workspace_bytes", "device_count", "launch_count", "resolve_cfg", "shard_range",
            "KERNELS", "KERNEL_IDS", "WEIGHTS", "HINTS", "VARIANTS"]

@@ -63,21 +63,35 @@ static int check_common(size_t n, int elem_bytes) {
 }
 
 // shared body of the six elementwise launchers
-static int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1, double s2,
-                     const b200_launch_cfg* cfg, void* stream) {
+static int check_bell(const b200_doorbell* bell, bool need_ticket) {
+  if (!bell) return B200_OK;
+  if (!bell->flag_host_mapped || (need_ticket && !bell->ticket) || bell->seq == 0) {
+    set_error("doorbell needs a flag address, a non-zero seq%s", need_ticket ? " and a ticket word" : "");
+    return B200_EINVAL;
+  }
+  return B200_OK;
+}
+
+int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1, double s2,
+              const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream) {
   if (int rc = check_common(n, elem_bytes)) return rc;
+  if (int rc = check_bell(bell, true)) return rc;
   const bool need_a = kernel != B200_MUL, need_b = kernel != B200_COPY, need_c = true;  // which arrays the op touches
   if (n > 0 && ((need_a && !a) || (need_b && !b) || (need_c && !c))) { set_error("null array pointer"); return B200_EINVAL; }
   const DeviceProps* props = current_device_props(nullptr);
   if (!props) return B200_ENODEVICE;
   EwCall call;
   if (int rc = resolve_cfg(kernel, n, elem_bytes, props->num_sms, props->l2_bytes, cfg, &call.r)) return rc;
-  if (n == 0) return B200_OK;
+  if (n == 0) {
+    if (bell) { set_error("a doorbell launch needs n > 0 (nothing would ring it)"); return B200_EINVAL; }
+    return B200_OK;
+  }
+  if (bell) { call.bell.ticket = bell->ticket; call.bell.flag = bell->flag_host_mapped; call.bell.seq = bell->seq; }
   call.a = a; call.b = b; call.c = c; call.n = n; call.elem_bytes = elem_bytes;
   call.s0 = s0; call.s1 = s1; call.s2 = s2;
   call.stream = static_cast<cudaStream_t>(stream);
 
-  if (kernel == B200_COPY && call.r.variant != B200_VARIANT_LDST) {
+  if (kernel == B200_COPY && call.r.variant != B200_VARIANT_LDST && !bell) {
     const size_t bytes = n * (size_t)elem_bytes;
     if (((uintptr_t)a | (uintptr_t)c) & 15) {
       // the async-proxy paths need 16-byte alignment: fall through to the register path
@@ -100,6 +114,26 @@ static int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_b
   }
   set_error("not an elementwise kernel: %d", kernel);
   return B200_EINVAL;
+}
+
+int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                      void* result_host_mapped, int world, int rank, unsigned long long seq, void* const* mailboxes,
+                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream) {
+  if (int rc = check_common(n, elem_bytes)) return rc;
+  if (int rc = check_bell(bell, false)) return rc;
+  if (!workspace || (n > 0 && (!a || !b))) { set_error("b200_launch_dot: null pointer"); return B200_EINVAL; }
+  const DeviceProps* props = current_device_props(nullptr);
+  if (!props) return B200_ENODEVICE;
+  DotCall call;
+  if (int rc = resolve_cfg(B200_DOT, n, elem_bytes, props->num_sms, props->l2_bytes, cfg, &call.r)) return rc;
+  call.a = a; call.b = b; call.n = n; call.elem_bytes = elem_bytes;
+  call.workspace = workspace; call.result_dev = result_dev; call.result_host = result_host_mapped;
+  call.p2p_world = world; call.p2p_rank = rank; call.p2p_seq = seq; call.p2p_mailboxes = mailboxes;
+  if (bell) { call.bell.flag = bell->flag_host_mapped; call.bell.seq = bell->seq; }
+  call.stream = static_cast<cudaStream_t>(stream);
+  call.g = make_geometry(a, b, nullptr, n, elem_bytes, call.r.vec_bytes, call.r.block, call.r.unroll, call.r.cache_hint);
+  call.grid = grid_for(call.r.grid_policy, call.g.ntiles, props->num_sms);
+  return launch_dot_impl(call);
 }
 
 }  // namespace b200
@@ -154,54 +188,53 @@ int b200_device_info(int device, int* num_sms, int* cc_major, int* cc_minor, siz
 
 int b200_launch_init(void* a, void* b, void* c, size_t n, int elem_bytes, double ia, double ib, double ic,
                      const b200_launch_cfg* cfg, void* stream) {
-  return launch_ew(B200_INIT, a, b, c, n, elem_bytes, ia, ib, ic, cfg, stream);
+  return launch_ew(B200_INIT, a, b, c, n, elem_bytes, ia, ib, ic, cfg, nullptr, stream);
 }
 int b200_launch_copy(const void* a, void* c, size_t n, int elem_bytes, const b200_launch_cfg* cfg, void* stream) {
-  return launch_ew(B200_COPY, const_cast<void*>(a), nullptr, c, n, elem_bytes, 0, 0, 0, cfg, stream);
+  return launch_ew(B200_COPY, const_cast<void*>(a), nullptr, c, n, elem_bytes, 0, 0, 0, cfg, nullptr, stream);
 }
 int b200_launch_mul(void* b, const void* c, size_t n, int elem_bytes, double scalar, const b200_launch_cfg* cfg,
                     void* stream) {
-  return launch_ew(B200_MUL, nullptr, b, const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, stream);
+  return launch_ew(B200_MUL, nullptr, b, const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, nullptr, stream);
 }
 int b200_launch_add(const void* a, const void* b, void* c, size_t n, int elem_bytes, const b200_launch_cfg* cfg,
                     void* stream) {
-  return launch_ew(B200_ADD, const_cast<void*>(a), const_cast<void*>(b), c, n, elem_bytes, 0, 0, 0, cfg, stream);
+  return launch_ew(B200_ADD, const_cast<void*>(a), const_cast<void*>(b), c, n, elem_bytes, 0, 0, 0, cfg, nullptr, stream);
 }
 int b200_launch_triad(void* a, const void* b, const void* c, size_t n, int elem_bytes, double scalar,
                       const b200_launch_cfg* cfg, void* stream) {
-  return launch_ew(B200_TRIAD, a, const_cast<void*>(b), const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, stream);
+  return launch_ew(B200_TRIAD, a, const_cast<void*>(b), const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, nullptr, stream);
 }
 int b200_launch_nstream(void* a, const void* b, const void* c, size_t n, int elem_bytes, double scalar,
                         const b200_launch_cfg* cfg, void* stream) {
-  return launch_ew(B200_NSTREAM, a, const_cast<void*>(b), const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, stream);
+  return launch_ew(B200_NSTREAM, a, const_cast<void*>(b), const_cast<void*>(c), n, elem_bytes, scalar, 0, 0, cfg, nullptr, stream);
 }
 
 size_t b200_dot_workspace_bytes(void) { return kDotWorkspaceBytes; }
 
-static int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
-                             void* result_host_mapped, int world, int rank, unsigned long long seq,
-                             void* const* mailboxes, const b200_launch_cfg* cfg, void* stream) {
-  if (int rc = check_common(n, elem_bytes)) return rc;
-  if (!workspace || (n > 0 && (!a || !b))) { set_error("b200_launch_dot: null pointer"); return B200_EINVAL; }
-  const DeviceProps* props = current_device_props(nullptr);
-  if (!props) return B200_ENODEVICE;
-  DotCall call;
-  if (int rc = resolve_cfg(B200_DOT, n, elem_bytes, props->num_sms, props->l2_bytes, cfg, &call.r)) return rc;
-  call.a = a; call.b = b; call.n = n; call.elem_bytes = elem_bytes;
-  call.workspace = workspace; call.result_dev = result_dev; call.result_host = result_host_mapped;
-  call.p2p_world = world; call.p2p_rank = rank; call.p2p_seq = seq; call.p2p_mailboxes = mailboxes;
-  call.stream = static_cast<cudaStream_t>(stream);
-  call.g = make_geometry(a, b, nullptr, n, elem_bytes, call.r.vec_bytes, call.r.block, call.r.unroll, call.r.cache_hint);
-  call.grid = grid_for(call.r.grid_policy, call.g.ntiles, props->num_sms);
-  return launch_dot_impl(call);
-}
-
 int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
                     void* result_host_mapped, const b200_launch_cfg* cfg, void* stream) {
-  return launch_dot_common(a, b, n, elem_bytes, workspace, result_dev, result_host_mapped, 0, 0, 0, nullptr, cfg, stream);
+  return launch_dot_common(a, b, n, elem_bytes, workspace, result_dev, result_host_mapped, 0, 0, 0, nullptr, cfg, nullptr, stream);
 }
 
-size_t b200_dot_mailbox_bytes(void) { return sizeof(MailSlot) * kMaxPeers; }
+int b200_launch_doorbell(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1, double s2,
+                         const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream) {
+  if (kernel == B200_DOT || kernel < 0 || kernel >= B200_NUM_KERNELS) {
+    set_error("b200_launch_doorbell: kernel id %d is not an elementwise kernel", kernel);
+    return B200_EINVAL;
+  }
+  if (!bell) { set_error("b200_launch_doorbell: null doorbell"); return B200_EINVAL; }
+  return launch_ew(kernel, a, b, c, n, elem_bytes, s0, s1, s2, cfg, bell, stream);
+}
+
+int b200_launch_dot_doorbell(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                             void* result_host_mapped, const b200_launch_cfg* cfg, const b200_doorbell* bell,
+                             void* stream) {
+  if (!bell) { set_error("b200_launch_dot_doorbell: null doorbell"); return B200_EINVAL; }
+  return launch_dot_common(a, b, n, elem_bytes, workspace, result_dev, result_host_mapped, 0, 0, 0, nullptr, cfg, bell, stream);
+}
+
+size_t b200_dot_mailbox_bytes(void) { return kMailboxBytes; }
 
 int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int elem_bytes, void* workspace,
                                   void* result_dev, void* result_host_mapped, int world, int rank,
@@ -209,7 +242,49 @@ int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int el
                                   void* stream) {
   if (world < 1 || world > kMaxPeers) { set_error("dot p2p: world must be 1..%d", kMaxPeers); return B200_EINVAL; }
   return launch_dot_common(a, b, n, elem_bytes, workspace, result_dev, result_host_mapped, world, rank, seq, mailboxes,
-                           cfg, stream);
+                           cfg, nullptr, stream);
+}
+
+// ---- cross-process peer memory (one process per GPU) ------------------------------------------
+int b200_dot_mailbox_create(void** mailbox) {
+  if (!mailbox) { set_error("b200_dot_mailbox_create: null argument"); return B200_EINVAL; }
+  if (!current_device_props(nullptr)) return B200_ENODEVICE;
+  void* p = nullptr;
+  B200_CUDA(cudaMalloc(&p, kMailboxBytes));  // its own allocation: cudaIpcGetMemHandle exports whole allocations
+  cudaError_t e = cudaMemset(p, 0, kMailboxBytes);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { cudaFree(p); return cuda_fail(e, "cudaMemset(mailbox)", __FILE__, __LINE__); }
+  *mailbox = p;
+  return B200_OK;
+}
+
+int b200_dot_mailbox_destroy(void* mailbox) {
+  if (mailbox) B200_CUDA(cudaFree(mailbox));
+  return B200_OK;
+}
+
+int b200_ipc_export(void* dev_ptr, void* handle_out) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == B200_IPC_HANDLE_BYTES, "handle size is part of the ABI");
+  if (!dev_ptr || !handle_out) { set_error("b200_ipc_export: null argument"); return B200_EINVAL; }
+  cudaIpcMemHandle_t h;
+  B200_CUDA(cudaIpcGetMemHandle(&h, dev_ptr));
+  memcpy(handle_out, &h, sizeof h);
+  return B200_OK;
+}
+
+int b200_ipc_open(const void* handle, void** dev_ptr) {
+  if (!handle || !dev_ptr) { set_error("b200_ipc_open: null argument"); return B200_EINVAL; }
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  void* p = nullptr;
+  B200_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *dev_ptr = p;
+  return B200_OK;
+}
+
+int b200_ipc_close(void* dev_ptr) {
+  if (dev_ptr) B200_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+  return B200_OK;
 }
 
 }  // extern "C"

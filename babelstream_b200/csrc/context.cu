@@ -71,7 +71,7 @@ struct NcclApi {
 
 enum { CMD_NONE = 0, CMD_KERNEL, CMD_READ, CMD_WRITE, CMD_QUIT };
 enum { COMBINE_AUTO = -1, COMBINE_NCCL = 0, COMBINE_HOST = 1, COMBINE_P2P = 2 };
-enum { SYNC_STREAM = 0, SYNC_SPIN = 1 };
+enum { SYNC_AUTO = -1, SYNC_STREAM = 0, SYNC_SPIN = 1, SYNC_DOORBELL = 2 };
 
 struct Shard {
   int dev = 0;
@@ -80,8 +80,10 @@ struct Shard {
   void *a = nullptr, *b = nullptr, *c = nullptr;
   void* dot_ws = nullptr;        // partials + ticket
   void* dot_dev = nullptr;       // 2 x 8 bytes: [0] this GPU's partial, [1] all-reduced value
-  void* dot_host = nullptr;      // mapped pinned, 8 bytes
+  void* dot_host = nullptr;      // mapped pinned, 64 bytes: [0,8) dot's sum, [8,16) the doorbell flag
   void* dot_host_dev = nullptr;  // device-side alias of dot_host
+  void* bell_ticket = nullptr;   // device word of the elementwise kernels' doorbell
+  unsigned long long bell_seq = 0;
   void* mailbox = nullptr;       // p2p combine: kMaxPeers slots in this GPU's HBM, written by the peers
   int rank = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -113,7 +115,10 @@ struct b200_ctx {
   // options
   b200_launch_cfg tune[B200_NUM_KERNELS];
   bool timing = false;
-  int sync_mode = SYNC_STREAM;
+  int sync_mode = SYNC_AUTO;
+  // one process per GPU (b200_join_group): this context is rank group_rank of group_world
+  int group_world = 1, group_rank = 0;
+  void* group_mailboxes[kMaxPeers] = {};
   int combine = COMBINE_AUTO;  // resolved by ensure_combine_ready: p2p if every pair has peer access, else nccl
   NcclApi nccl;
   bool nccl_ready = false;
@@ -155,17 +160,55 @@ static int stream_wait(b200_ctx* ctx, Shard* s) {
   return B200_OK;
 }
 
+// Wait for the doorbell of the launch just issued (kernels.cuh): spin on the host word the kernel's
+// last block writes.  Every 64 Ki polls the stream is queried, so that a failed launch or a faulting
+// kernel ends in an error instead of a hang.
+static int bell_wait(Shard* s, unsigned long long seq) {
+  const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(static_cast<char*>(s->dot_host) + 8);
+  for (unsigned spins = 1;; ++spins) {
+    if (__atomic_load_n(flag, __ATOMIC_ACQUIRE) == seq) return B200_OK;
+    if ((spins & 0xffffu) == 0) {
+      const cudaError_t e = cudaStreamQuery(s->stream);
+      if (e == cudaSuccess) {
+        if (__atomic_load_n(flag, __ATOMIC_ACQUIRE) == seq) return B200_OK;
+        set_error("kernel finished without ringing its doorbell (seq %llu)", seq);
+        return B200_ECUDA;
+      }
+      if (e != cudaErrorNotReady) return cuda_fail(e, "cudaStreamQuery(stream)", __FILE__, __LINE__);
+    }
+    B200_PAUSE();
+  }
+}
+
+// Does this call wait on a doorbell?  auto: dot only.  Measured on B200 (profiles/r01/wait_modes.md):
+// dot's blocking call gets 1.3-1.9 us shorter at every size, because the host no longer waits for the
+// end-of-kernel flush of dot's own write into host memory; the ticket is one dot takes anyway.  The
+// elementwise kernels have no such write, the ring saves them 0.2 us at best, and the per-block ticket
+// costs 1-3 us as soon as there are ~1000 blocks (same-address atomics drain at ~3 ns each) -- so they
+// ring only when asked to (sync=doorbell).
+static bool use_doorbell(const b200_ctx* ctx, const Shard* s, int kernel) {
+  if (ctx->timing || s->count == 0) return false;
+  if (kernel == B200_DOT && ctx->ngpus > 1 && ctx->combine == COMBINE_NCCL) return false;  // the all-reduce follows
+  if (ctx->sync_mode == SYNC_DOORBELL) return true;
+  return ctx->sync_mode == SYNC_AUTO && kernel == B200_DOT;
+}
+
 // Launch one kernel on one shard (device already current).  No synchronisation.
-static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd) {
+static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd, const b200_doorbell* bell) {
   const int eb = ctx->elem_bytes;
   const b200_launch_cfg* cfg = &ctx->tune[cmd.kernel];
   void* st = s->stream;
   if (cmd.kernel == B200_DOT) {
     const bool single = ctx->ngpus == 1;
+    if (single && ctx->group_world > 1) {
+      // one process per GPU: same fused kernel, the peers' mailboxes are IPC mappings
+      return launch_dot_common(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, s->dot_host_dev, ctx->group_world,
+                               ctx->group_rank, cmd.seq, ctx->group_mailboxes, cfg, bell, st);
+    }
     if (!single && ctx->combine == COMBINE_P2P) {
       // fused: partial + all-reduce over peer memory in ONE launch; an empty shard still takes part
-      return b200_launch_dot_allreduce_p2p(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, s->dot_host_dev, ctx->ngpus,
-                                           s->rank, cmd.seq, ctx->mailboxes, cfg, st);
+      return launch_dot_common(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, s->dot_host_dev, ctx->ngpus, s->rank,
+                               cmd.seq, ctx->mailboxes, cfg, bell, st);
     }
     // single GPU: the kernel writes the sum straight into mapped host memory (zero-copy)
     if (s->count == 0) {
@@ -174,19 +217,13 @@ static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd) {
       return B200_OK;
     }
     const bool to_host = single || ctx->combine == COMBINE_HOST;
-    return b200_launch_dot(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, to_host ? s->dot_host_dev : nullptr, cfg, st);
+    return launch_dot_common(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, to_host ? s->dot_host_dev : nullptr, 0, 0, 0,
+                             nullptr, cfg, bell, st);
   }
   if (s->count == 0) return B200_OK;
-  switch (cmd.kernel) {
-    case B200_INIT: return b200_launch_init(s->a, s->b, s->c, s->count, eb, cmd.s0, cmd.s1, cmd.s2, cfg, st);
-    case B200_COPY: return b200_launch_copy(s->a, s->c, s->count, eb, cfg, st);
-    case B200_MUL: return b200_launch_mul(s->b, s->c, s->count, eb, cmd.s0, cfg, st);
-    case B200_ADD: return b200_launch_add(s->a, s->b, s->c, s->count, eb, cfg, st);
-    case B200_TRIAD: return b200_launch_triad(s->a, s->b, s->c, s->count, eb, cmd.s0, cfg, st);
-    case B200_NSTREAM: return b200_launch_nstream(s->a, s->b, s->c, s->count, eb, cmd.s0, cfg, st);
-  }
-  set_error("unknown kernel id %d", cmd.kernel);
-  return B200_EINVAL;
+  if (cmd.kernel < 0 || cmd.kernel >= B200_NUM_KERNELS) { set_error("unknown kernel id %d", cmd.kernel); return B200_EINVAL; }
+  // launch_ew ignores the arrays a kernel does not touch
+  return launch_ew(cmd.kernel, s->a, s->b, s->c, s->count, eb, cmd.s0, cmd.s1, cmd.s2, cfg, bell, st);
 }
 
 // Everything one GPU does for one command, including the wait.  Runs on the worker thread of the
@@ -202,7 +239,14 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
   if (cmd.kind == CMD_KERNEL) {
     if (ctx->hostprof) t1 = clk::now();
     if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev0, s->stream));
-    if (int rc = shard_launch(ctx, s, cmd)) return rc;
+    b200_doorbell bell_store, *bell = nullptr;
+    if (use_doorbell(ctx, s, cmd.kernel)) {
+      bell_store.ticket = s->bell_ticket;
+      bell_store.flag_host_mapped = static_cast<char*>(s->dot_host_dev) + 8;
+      bell_store.seq = ++s->bell_seq;
+      bell = &bell_store;
+    }
+    if (int rc = shard_launch(ctx, s, cmd, bell)) return rc;
     if (ctx->hostprof) t2 = clk::now();
     if (cmd.kernel == B200_DOT && ctx->ngpus > 1 && ctx->combine == COMBINE_NCCL) {
       // the one collective of the whole benchmark: G partial sums -> every GPU holds the total
@@ -212,7 +256,7 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
       if (g == 0) B200_CUDA(cudaMemcpyAsync(s->dot_host, buf + 8, eb, cudaMemcpyDeviceToHost, s->stream));
     }
     if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev1, s->stream));
-    if (int rc = stream_wait(ctx, s)) return rc;
+    if (int rc = bell ? bell_wait(s, bell->seq) : stream_wait(ctx, s)) return rc;
     if (ctx->hostprof && g == 0) {
       const clk::time_point t3 = clk::now();
       ctx->prof_ns[0] += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count();
@@ -321,7 +365,7 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
   } else if (key == "timing") {
     ctx->timing = (val == "1" || val == "on" || val == "true");
   } else if (key == "sync") {
-    ctx->sync_mode = val == "spin" ? SYNC_SPIN : SYNC_STREAM;
+    ctx->sync_mode = val == "spin" ? SYNC_SPIN : val == "stream" ? SYNC_STREAM : val == "doorbell" ? SYNC_DOORBELL : SYNC_AUTO;
   } else if (key == "tune") {
     // "<kernel>:<fields>;<kernel>:<fields>"   kernel "all" applies to the six elementwise kernels
     size_t pos = 0;
@@ -459,7 +503,7 @@ void b200_destroy(b200_ctx* ctx) {
     if (s->stream) cudaStreamDestroy(s->stream);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
-    cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox);
+    cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox); cudaFree(s->bell_ticket);
     if (s->dot_host) cudaFreeHost(s->dot_host);
     delete s;
   }
@@ -536,11 +580,14 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
     cu(cudaMalloc(&s->c, alloc), "cudaMalloc(c)");
     cu(cudaMalloc(&s->dot_ws, kDotWorkspaceBytes), "cudaMalloc(dot workspace)");
     cu(cudaMalloc(&s->dot_dev, 16), "cudaMalloc(dot scalars)");
-    cu(cudaHostAlloc(&s->dot_host, 8, cudaHostAllocMapped | cudaHostAllocPortable), "cudaHostAlloc(dot result)");
+    cu(cudaMalloc(&s->bell_ticket, 256), "cudaMalloc(doorbell ticket)");
+    cu(cudaHostAlloc(&s->dot_host, 64, cudaHostAllocMapped | cudaHostAllocPortable), "cudaHostAlloc(dot result)");
     if (rc) return fail(rc);
+    memset(s->dot_host, 0, 64);
     cu(cudaHostGetDevicePointer(&s->dot_host_dev, s->dot_host, 0), "cudaHostGetDevicePointer");
     cu(cudaMemsetAsync(s->dot_ws, 0, kDotWorkspaceBytes, s->stream), "cudaMemsetAsync");
     cu(cudaMemsetAsync(s->dot_dev, 0, 16, s->stream), "cudaMemsetAsync");
+    cu(cudaMemsetAsync(s->bell_ticket, 0, 256, s->stream), "cudaMemsetAsync");
     cu(cudaStreamSynchronize(s->stream), "cudaStreamSynchronize");
     if (rc) return fail(rc);
   }
@@ -559,6 +606,23 @@ int b200_set_option(b200_ctx* ctx, const char* key, const char* value) {
   if (!ctx || !key || !value) { set_error("b200_set_option: null argument"); return B200_EINVAL; }
   if (int rc = apply_option(ctx, key, value)) return rc;
   return ensure_combine_ready(ctx);  // e.g. dot_combine switched to nccl or p2p: bring it up now
+}
+
+int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes) {
+  if (!ctx) { set_error("null context"); return B200_EINVAL; }
+  if (ctx->ngpus != 1) { set_error("b200_join_group: the context must own exactly one GPU (it has %d)", ctx->ngpus); return B200_EINVAL; }
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || (world > 1 && !mailboxes)) {
+    set_error("b200_join_group: bad world/rank (%d/%d; at most %d ranks)", world, rank, kMaxPeers);
+    return B200_EINVAL;
+  }
+  for (int g = 0; g < kMaxPeers; g++) {
+    ctx->group_mailboxes[g] = (world > 1 && g < world) ? mailboxes[g] : nullptr;
+    if (world > 1 && g < world && !mailboxes[g]) { set_error("b200_join_group: mailbox %d is null", g); ctx->group_world = 1; return B200_EINVAL; }
+  }
+  ctx->group_world = world;
+  ctx->group_rank = rank;
+  ctx->dot_seq = 0;  // every rank counts its dot calls from the moment it joins
+  return B200_OK;
 }
 
 int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
@@ -589,6 +653,15 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
     if (v) { snprintf(line, sizeof line, " (NCCL %d)", v); out += line; }
     out += "\n";
   }
+  if (ctx->group_world > 1) {
+    snprintf(line, sizeof line, "  rank %d of %d processes; dot: fused peer-memory all-reduce over IPC mailboxes\n", ctx->group_rank,
+             ctx->group_world);
+    out += line;
+  }
+  const char* sync_names[] = {"auto (dot: doorbell rung by the kernel; elementwise: cudaStreamSynchronize)", "cudaStreamSynchronize",
+                              "cudaStreamQuery spin", "doorbell"};
+  snprintf(line, sizeof line, "  wait: %s\n", sync_names[ctx->sync_mode + 1]);
+  out += line;
   snprintf(buf, (size_t)buflen, "%s", out.c_str());
   return B200_OK;
 }

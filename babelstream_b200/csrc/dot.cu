@@ -9,22 +9,23 @@ namespace b200 {
   B200_DOT_CASE(16, 1, H) B200_DOT_CASE(16, 2, H) B200_DOT_CASE(16, 4, H) B200_DOT_CASE(16, 8, H) \
   B200_DOT_CASE(32, 1, H) B200_DOT_CASE(32, 2, H) B200_DOT_CASE(32, 4, H)
 
-template <typename T, bool FUSED, bool TICKET>
+template <typename T, bool FUSED, int MODE>
 static int launch_dot_typed(const DotCall& call) {
   using Kernel = void (*)(const DotArgs);
   Kernel k = nullptr;
   const int vb = call.g.vec_bytes, u = call.g.unroll, h = call.g.cache_hint;
 #define B200_DOT_CASE(VB, U, H) \
-  if (vb == VB && u == U && h == H) k = dot_kernel<T, VB, U, H, FUSED, TICKET>;
+  if (vb == VB && u == U && h == H) k = dot_kernel<T, VB, U, H, FUSED, MODE>;
   B200_DOT_FOR_HINT(1) B200_DOT_FOR_HINT(2) B200_DOT_FOR_HINT(3) B200_DOT_FOR_HINT(4) B200_DOT_FOR_HINT(5)
-  if constexpr (sizeof(T) == 4) { if (vb == 4 && u == 4 && h == 1) k = dot_kernel<T, 4, 4, 1, FUSED, TICKET>; }
+  if constexpr (sizeof(T) == 4) { if (vb == 4 && u == 4 && h == 1) k = dot_kernel<T, 4, 4, 1, FUSED, MODE>; }
 #undef B200_DOT_CASE
   if (!k) {
     set_error("no dot kernel compiled for vec_bytes=%d unroll=%d cache_hint=%d", vb, u, h);
     return B200_EUNSUPPORTED;
   }
-  if (call.r.block > dot_max_block(vb, u)) {
-    set_error("dot: block %d too large for vec_bytes=%d unroll=%d (max %d)", call.r.block, vb, u, dot_max_block(vb, u));
+  if (call.r.block > dot_block_bound(vb, u, MODE)) {
+    set_error("dot: block %d too large for vec_bytes=%d unroll=%d%s (max %d)", call.r.block, vb, u,
+              MODE == DOT_TICKET_P2P ? " with the fused peer-memory all-reduce" : "", dot_block_bound(vb, u, MODE));
     return B200_EINVAL;
   }
   DotArgs args;
@@ -33,17 +34,18 @@ static int launch_dot_typed(const DotCall& call) {
   args.ticket = reinterpret_cast<unsigned int*>(static_cast<char*>(call.workspace) + kDotMaxBlocks * 8);
   args.result_dev = call.result_dev; args.result_host = call.result_host;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
+  args.bell_flag = static_cast<unsigned long long*>(call.bell.flag); args.bell_seq = call.bell.seq;
   args.p2p.world = call.p2p_world; args.p2p.rank = call.p2p_rank; args.p2p.seq = call.p2p_seq;
   for (int g = 0; g < kMaxPeers; g++)
     args.p2p.mailbox[g] = (call.p2p_world > 1 && g < call.p2p_world) ? static_cast<MailSlot*>(call.p2p_mailboxes[g]) : nullptr;
   k<<<call.grid, call.r.block, 0, call.stream>>>(args);
   count_launch();
   B200_CUDA(cudaPeekAtLastError());
-  if (!TICKET) {
+  if (MODE == DOT_TWO_PASS) {
     // same block size as pass 1, so that both variants add the partials in the same order
     dot_final_kernel<T><<<1, call.r.block, 0, call.stream>>>(static_cast<const T*>(call.workspace), call.grid,
                                                       static_cast<T*>(call.result_dev),
-                                                      static_cast<T*>(call.result_host));
+                                                      static_cast<T*>(call.result_host), args.bell_flag, args.bell_seq);
     count_launch();
     B200_CUDA(cudaPeekAtLastError());
   }
@@ -64,12 +66,16 @@ int launch_dot_impl(const DotCall& call) {
     set_error("dot grid %u exceeds the workspace capacity of %d blocks", call.grid, kDotMaxBlocks);
     return B200_EINVAL;
   }
-  if (call.elem_bytes == 8) {
-    if (fused) return ticket ? launch_dot_typed<double, true, true>(call) : launch_dot_typed<double, true, false>(call);
-    return ticket ? launch_dot_typed<double, false, true>(call) : launch_dot_typed<double, false, false>(call);
+  const int mode = call.p2p_world > 1 ? DOT_TICKET_P2P : ticket ? DOT_TICKET : DOT_TWO_PASS;
+#define B200_DOT_DISPATCH(T)                                                                                   \
+  switch (mode) {                                                                                              \
+    case DOT_TWO_PASS: return fused ? launch_dot_typed<T, true, DOT_TWO_PASS>(call) : launch_dot_typed<T, false, DOT_TWO_PASS>(call); \
+    case DOT_TICKET: return fused ? launch_dot_typed<T, true, DOT_TICKET>(call) : launch_dot_typed<T, false, DOT_TICKET>(call);       \
+    default: return fused ? launch_dot_typed<T, true, DOT_TICKET_P2P>(call) : launch_dot_typed<T, false, DOT_TICKET_P2P>(call);     \
   }
-  if (fused) return ticket ? launch_dot_typed<float, true, true>(call) : launch_dot_typed<float, true, false>(call);
-  return ticket ? launch_dot_typed<float, false, true>(call) : launch_dot_typed<float, false, false>(call);
+  if (call.elem_bytes == 8) { B200_DOT_DISPATCH(double) }
+  B200_DOT_DISPATCH(float)
+#undef B200_DOT_DISPATCH
 }
 
 }  // namespace b200

@@ -55,6 +55,13 @@ struct Geometry {
 Geometry make_geometry(const void* p0, const void* p1, const void* p2, size_t n, int elem_bytes, int vec_bytes,
                        int block, int unroll, int cache_hint);
 
+// Completion doorbell of a launch (see kernels.cuh); flag == nullptr: none.
+struct Bell {
+  void* ticket = nullptr;      // device word, zero between launches
+  void* flag = nullptr;        // device-visible address of a mapped pinned host word
+  unsigned long long seq = 0;  // value the kernel stores when its last block has finished
+};
+
 // Per-op elementwise launchers (one translation unit each, so they compile in parallel).
 struct EwCall {
   void *a, *b, *c;
@@ -65,6 +72,7 @@ struct EwCall {
   Geometry g;
   unsigned grid;
   cudaStream_t stream;
+  Bell bell;
 };
 int launch_ew_init(const EwCall& call);
 int launch_ew_copy(const EwCall& call);
@@ -84,12 +92,20 @@ struct DotCall {
   int p2p_world = 0, p2p_rank = 0;
   unsigned long long p2p_seq = 0;
   void* const* p2p_mailboxes = nullptr;
+  Bell bell;  // only .flag and .seq are used: dot has its own ticket
   Resolved r;
   Geometry g;
   unsigned grid;
   cudaStream_t stream;
 };
 int launch_dot_impl(const DotCall& call);
+
+// shared bodies of the LEVEL 1 launchers (api.cu), also called by LEVEL 2 with a doorbell
+int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1, double s2,
+              const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream);
+int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                      void* result_host_mapped, int world, int rank, unsigned long long seq, void* const* mailboxes,
+                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream);
 
 int launch_copy_bulk(const void* src, void* dst, size_t bytes, const Resolved& r, const DeviceProps& props,
                      cudaStream_t stream);

@@ -189,6 +189,41 @@ __device__ __forceinline__ Words<VB> pack(const Elems<T, VB>& e) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Completion doorbell.  A blocking caller normally learns that a kernel has finished from
+// cudaStreamSynchronize, i.e. from the semaphore the front end releases after the grid has drained
+// and its caches are flushed, plus the driver's own bookkeeping: 2-3 us after the last store.  With
+// a doorbell the kernel rings the host itself: every block takes a ticket once its stores are
+// fenced, and the block that takes the last one writes `seq` to a word of mapped pinned host memory
+// that the caller spins on.  Stream order still holds for whatever is enqueued next, so "results are
+// complete when the call returns" (src/Stream.h:36) is kept.  Default for dot, which takes a ticket
+// anyway and whose result is itself a write into host memory (the call gets 1.3-1.9 us shorter);
+// opt-in for the elementwise kernels, where ~1000 same-address tickets cost more than the ring saves.
+// ------------------------------------------------------------------------------------------------
+struct Doorbell {
+  unsigned int* ticket;            // device word, zero between launches
+  unsigned long long* flag;        // device-visible address of mapped pinned host memory, or nullptr
+  unsigned long long seq;          // value to store
+};
+
+__device__ __forceinline__ void ring_host(unsigned long long* flag, unsigned long long seq) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(seq) : "memory");
+}
+
+// Block-level: call with all threads once the block's stores have been issued.
+__device__ __forceinline__ void doorbell_block_done(const Doorbell& bell) {
+  __syncthreads();  // every thread's stores are issued ...
+  if (threadIdx.x == 0) {
+    __threadfence();  // ... and ordered before the ticket
+    const unsigned t = atomicAdd(bell.ticket, 1u);
+    if (t == gridDim.x - 1) {
+      *bell.ticket = 0u;  // ready for the next launch (stream order separates the launches)
+      __threadfence();    // acquire side: the other blocks' stores are visible before the host is told
+      ring_host(bell.flag, bell.seq);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Elementwise kernels.  One template for init/copy/mul/add/triad/nstream.
 //
 // Geometry: the arrays are addressed from element `head` (0 <= head < VB/sizeof(T), chosen by the
@@ -206,6 +241,7 @@ struct EwArgs {
   unsigned long long ntiles;  // ceil(nvec / (blockDim.x * UNROLL))
   unsigned long long n;       // total elements
   unsigned int head;          // leading scalar elements
+  Doorbell bell;              // flag == nullptr: none
 };
 
 template <typename T, int OP, bool FUSED>
@@ -303,6 +339,7 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
       ew_scalar<T, OP, FUSED>(a, b, c, i, s0, s1, s2);
     }
   }
+  if (args.bell.flag) doorbell_block_done(args.bell);  // grid-uniform
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -362,6 +399,12 @@ struct alignas(16) MailSlot {
   unsigned long long seq;
   unsigned long long bits;
 };
+// A mailbox is TWO banks of kMaxPeers slots, used alternately (bank = seq & 1).  GPU A can only start
+// call k+2 after it has finished call k+1, which needed B's partial of k+1, which B sent after it had
+// read everything of call k: so a slot of bank k&1 is never overwritten while a peer may still read it,
+// however far the GPUs drift apart between calls.
+constexpr int kMailBanks = 2;
+constexpr size_t kMailboxBytes = sizeof(MailSlot) * kMaxPeers * kMailBanks;
 
 __device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -401,16 +444,23 @@ template <> __device__ __forceinline__ float from_bits<float>(unsigned long long
 
 // Called by warp 0 of the last block; `mine` is this GPU's partial.  Returns the all-reduced sum
 // (identical on every GPU) in every lane.
+// Only the MODE == 2 instantiations of dot_kernel contain this code: inlined or not, it raises the
+// kernel's register allocation from 38 to 42, which drops the residency of 512-thread blocks from 3
+// to 2 per SM (-3.5 % at 2^29) -- so single-GPU, NCCL and host-combine runs use the lean kernel, and
+// the MODE 2 kernel is register-capped by its launch bound instead (the spills land in this
+// once-per-launch code).  `pp` points INTO the __grid_constant__ parameter block: nothing is copied.
 template <typename T>
-__device__ __forceinline__ T p2p_allreduce_warp(const P2PArgs& p, T mine) {
+__device__ __noinline__ T p2p_allreduce_warp(const P2PArgs* pp, T mine) {
+  const P2PArgs& p = *pp;
   const int lane = threadIdx.x & 31;
   bool ok = true;
   T got = T(0);
+  const int bank = (int)(p.seq & 1ull) * kMaxPeers;
   if (lane < p.world) {
-    MailSlot* dst = p.mailbox[lane] + p.rank;   // my slot in GPU `lane`'s mailbox
+    MailSlot* dst = p.mailbox[lane] + bank + p.rank;   // my slot in GPU `lane`'s mailbox
     st_relaxed_sys(&dst->bits, to_bits<T>(mine));
     st_release_sys(&dst->seq, p.seq);           // value is visible before the sequence number
-    const MailSlot* src = p.mailbox[p.rank] + lane;  // GPU `lane`'s slot in my mailbox (local HBM)
+    const MailSlot* src = p.mailbox[p.rank] + bank + lane;  // GPU `lane`'s slot in my mailbox (local HBM)
     const unsigned long long t0 = global_timer_ns();
     while (ld_acquire_sys(&src->seq) != p.seq) {
       if (global_timer_ns() - t0 > 2000000000ull) { ok = false; break; }
@@ -432,6 +482,8 @@ struct DotArgs {
   void* result_host;     // mapped pinned, may be null
   unsigned long long nvec, ntiles, n;
   unsigned int head;
+  unsigned long long* bell_flag;  // doorbell (mapped pinned host word) rung after the result is stored, or nullptr
+  unsigned long long bell_seq;
   P2PArgs p2p;           // world <= 1: plain single-GPU dot
 };
 
@@ -439,9 +491,19 @@ struct DotArgs {
 // (2 operands x 128 bytes per thread), which therefore run with at most 512 threads.
 constexpr int dot_max_block(int vb, int unroll) { return vb * unroll >= 128 ? 512 : 1024; }
 
-template <typename T, int VB, int UNROLL, int HINT, bool FUSED, bool TICKET>
-__global__ void __launch_bounds__(dot_max_block(VB, UNROLL))
-dot_kernel(const DotArgs args) {
+// MODE: how the block partials become the result
+enum DotMode : int { DOT_TWO_PASS = 0,    // partials only; dot_final_kernel follows
+                     DOT_TICKET = 1,      // the last block to finish runs the second pass
+                     DOT_TICKET_P2P = 2 };// ... and then the all-reduce over peer memory
+// the P2P instantiation runs with at most 512 threads and must keep 3 blocks of them resident
+constexpr int dot_block_bound(int vb, int unroll, int mode) {
+  return mode == DOT_TICKET_P2P ? 512 : dot_max_block(vb, unroll);
+}
+constexpr int dot_min_blocks(int vb, int unroll, int mode) { return (mode == DOT_TICKET_P2P && vb * unroll <= 32) ? 3 : 1; }
+
+template <typename T, int VB, int UNROLL, int HINT, bool FUSED, int MODE>
+__global__ void __launch_bounds__(dot_block_bound(VB, UNROLL, MODE), dot_min_blocks(VB, UNROLL, MODE))
+dot_kernel(const __grid_constant__ DotArgs args) {
   constexpr int EPV = VB / (int)sizeof(T);
   __shared__ T scratch[32];
   __shared__ bool is_last;
@@ -508,7 +570,7 @@ dot_kernel(const DotArgs args) {
   T* const partials = static_cast<T*>(args.partials);
   if (threadIdx.x == 0) partials[blockIdx.x] = sum;
 
-  if constexpr (TICKET) {
+  if constexpr (MODE != DOT_TWO_PASS) {
     if (threadIdx.x == 0) {
       __threadfence();  // partial visible before the ticket is taken
       const unsigned t = atomicAdd(args.ticket, 1u);
@@ -519,14 +581,15 @@ dot_kernel(const DotArgs args) {
     if (is_last) {
       T v = dot_second_pass<T>(partials, gridDim.x, scratch);
       if (threadIdx.x == 0) *args.ticket = 0u;  // ready for the next launch
-      if (args.p2p.world > 1) {                 // fused all-reduce over peer memory (block-uniform branch)
+      if constexpr (MODE == DOT_TICKET_P2P) {   // fused all-reduce over peer memory
         if (threadIdx.x == 0) scratch[0] = v;
         __syncthreads();
-        if (threadIdx.x < 32) v = p2p_allreduce_warp<T>(args.p2p, scratch[0]);
+        if (threadIdx.x < 32) v = p2p_allreduce_warp<T>(&args.p2p, scratch[0]);
       }
       if (threadIdx.x == 0) {
         if (args.result_dev) *static_cast<T*>(args.result_dev) = v;
         if (args.result_host) *static_cast<T*>(args.result_host) = v;
+        if (args.bell_flag) ring_host(args.bell_flag, args.bell_seq);  // release: after the result
       }
     }
   }
@@ -534,12 +597,14 @@ dot_kernel(const DotArgs args) {
 
 template <typename T>
 __global__ void __launch_bounds__(1024)
-dot_final_kernel(const T* partials, unsigned nparts, T* result_dev, T* result_host) {
+dot_final_kernel(const T* partials, unsigned nparts, T* result_dev, T* result_host, unsigned long long* bell_flag,
+                 unsigned long long bell_seq) {
   __shared__ T scratch[32];
   const T v = dot_second_pass<T>(partials, nparts, scratch);
   if (threadIdx.x == 0) {
     if (result_dev) *result_dev = v;
     if (result_host) *result_host = v;
+    if (bell_flag) ring_host(bell_flag, bell_seq);
   }
 }
 

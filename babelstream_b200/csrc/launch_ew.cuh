@@ -37,6 +37,9 @@ int launch_ew_typed(const EwCall& call) {
   EwArgs args;
   args.a = call.a; args.b = call.b; args.c = call.c;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
+  args.bell.ticket = static_cast<unsigned int*>(call.bell.ticket);
+  args.bell.flag = static_cast<unsigned long long*>(call.bell.flag);
+  args.bell.seq = call.bell.seq;
   k<<<call.grid, call.r.block, 0, call.stream>>>(args, (T)call.s0, (T)call.s1, (T)call.s2);
   count_launch();
   B200_CUDA(cudaPeekAtLastError());

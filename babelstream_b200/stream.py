@@ -29,6 +29,9 @@ VARIANTS = {"auto": 0, "ldst": 1, "bulk": 2, "tma": 3, "two_pass": 1, "ticket": 
 START_A, START_B, START_C, START_SCALAR = 0.1, 0.2, 0.0, 0.4  # src/Stream.h:24-27
 
 
+IPC_HANDLE_BYTES = 64  # B200_IPC_HANDLE_BYTES
+
+
 class B200Error(RuntimeError):
     def __init__(self, code: int, message: str):
         super().__init__(f"[b200 error {code}] {message}")
@@ -56,6 +59,11 @@ class LaunchCfg(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+
+
+class Doorbell(C.Structure):
+    """b200_doorbell: the kernel's last block stores `seq` to a mapped pinned host word."""
+    _fields_ = [("ticket", C.c_void_p), ("flag_host_mapped", C.c_void_p), ("seq", C.c_ulonglong)]
 
 
 def lib_path() -> str:
@@ -98,6 +106,14 @@ def lib() -> C.CDLL:
         "b200_launch_dot": (ci, [vp, vp, sz, ci, vp, vp, vp, cfgp, vp]),
         "b200_dot_mailbox_bytes": (sz, []),
         "b200_launch_dot_allreduce_p2p": (ci, [vp, vp, sz, ci, vp, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
+        "b200_launch_doorbell": (ci, [ci, vp, vp, vp, sz, ci, d, d, d, cfgp, C.POINTER(Doorbell), vp]),
+        "b200_launch_dot_doorbell": (ci, [vp, vp, sz, ci, vp, vp, vp, cfgp, C.POINTER(Doorbell), vp]),
+        "b200_dot_mailbox_create": (ci, [C.POINTER(vp)]),
+        "b200_dot_mailbox_destroy": (ci, [vp]),
+        "b200_ipc_export": (ci, [vp, vp]),
+        "b200_ipc_open": (ci, [vp, C.POINTER(vp)]),
+        "b200_ipc_close": (ci, [vp]),
+        "b200_join_group": (ci, [vp, ci, ci, C.POINTER(vp)]),
         "b200_create": (vp, [ci, ci, sz, ci, C.POINTER(ci)]),
         "b200_destroy": (None, [vp]),
         "b200_set_option": (ci, [vp, cp, cp]),
@@ -208,6 +224,62 @@ def launch_dot_allreduce_p2p(a: int, b: int, n: int, elem_bytes: int, workspace:
                                                C.c_void_p(stream)))
 
 
+def launch_doorbell(kernel: str, a: int, b: int, c: int, n: int, elem_bytes: int, bell: Doorbell, *,
+                    scalar: float = START_SCALAR, init=(START_A, START_B, START_C), cfg: LaunchCfg | None = None,
+                    stream: int = 0) -> None:
+    """LEVEL 1: an elementwise kernel whose last block rings `bell` (see b200_doorbell).  Asynchronous."""
+    s0, s1, s2 = init if kernel == "init" else (scalar, 0.0, 0.0)
+    _check(lib().b200_launch_doorbell(KERNEL_IDS[kernel], a or None, b or None, c or None, n, elem_bytes, s0, s1, s2,
+                                      C.byref(cfg) if cfg is not None else None, C.byref(bell), C.c_void_p(stream)))
+
+
+def launch_dot_doorbell(a: int, b: int, n: int, elem_bytes: int, workspace: int, result_dev: int, bell: Doorbell, *,
+                        result_host_mapped: int = 0, cfg: LaunchCfg | None = None, stream: int = 0) -> None:
+    _check(lib().b200_launch_dot_doorbell(a, b, n, elem_bytes, workspace, result_dev or None, result_host_mapped or None,
+                                          C.byref(cfg) if cfg is not None else None, C.byref(bell), C.c_void_p(stream)))
+
+
+class Mailbox:
+    """This process's dot mailbox on the current device plus, once `connect`ed, its peers' mailboxes.
+
+    One process per GPU (torchrun): ``mb = Mailbox(); handles = all_gather(mb.handle);
+    ptrs = mb.connect(handles, rank)`` -- ``ptrs`` is what ``launch_dot_allreduce_p2p`` and
+    ``B200Stream.join_group`` take.  The exchange of the 64-byte handles is the caller's business
+    (``babelstream_b200.group.connect_mailboxes`` does it with torch.distributed).
+    """
+
+    def __init__(self):
+        p = C.c_void_p()
+        _check(lib().b200_dot_mailbox_create(C.byref(p)))
+        self.ptr = p.value
+        h = C.create_string_buffer(IPC_HANDLE_BYTES)
+        _check(lib().b200_ipc_export(self.ptr, h))
+        self.handle = h.raw
+        self._opened = []
+        self.ptrs = None
+
+    def connect(self, handles, rank: int):
+        ptrs = []
+        for g, h in enumerate(handles):
+            if g == rank:
+                ptrs.append(self.ptr)
+                continue
+            p = C.c_void_p()
+            _check(lib().b200_ipc_open(C.create_string_buffer(bytes(h), IPC_HANDLE_BYTES), C.byref(p)))
+            self._opened.append(p.value)
+            ptrs.append(p.value)
+        self.ptrs = ptrs
+        return ptrs
+
+    def close(self):
+        for p in self._opened:
+            lib().b200_ipc_close(p)
+        self._opened = []
+        if self.ptr:
+            lib().b200_dot_mailbox_destroy(self.ptr)
+            self.ptr = None
+
+
 class B200Stream:
     """Host-side mirror of ``Stream<T>`` (src/Stream.h:29-49) over LEVEL 2 of the C ABI.
 
@@ -311,6 +383,11 @@ class B200Stream:
 
     def set_option(self, key: str, value) -> None:
         _check(lib().b200_set_option(self._h, key.encode(), str(value).encode()))
+
+    def join_group(self, world: int, rank: int, mailboxes) -> None:
+        """One process per GPU: dot() returns the all-rank sum from here on (fused peer-memory all-reduce)."""
+        boxes = (C.c_void_p * max(1, len(mailboxes)))(*mailboxes)
+        _check(lib().b200_join_group(self._h, world, rank, boxes))
 
     def describe(self) -> str:
         buf = C.create_string_buffer(4096)

@@ -6,8 +6,10 @@
 
 Workload (BASELINE.json configs[1]): fp64, 2^25 elements PER GPU, all six kernels.  One STEP is one
 pass of the driver's kernel sequence  copy, mul, add, triad, dot, nstream  (src/benchmark.h:32-39)
-over the rank's contiguous shard; with N > 1 the step's dot partials are combined by one NCCL
-all-reduce of one element.  Scaling is weak (per-GPU work fixed, no data-path collective for the
+over the rank's contiguous shard; with N > 1 the step's dot partials are combined INSIDE the dot
+kernel by the fused peer-memory all-reduce (mailboxes in every GPU's HBM, mapped into the other ranks
+through CUDA IPC, written over NVLink; no NCCL on the data path -- NCCL is the fallback when the
+mailboxes cannot be mapped).  Scaling is weak (per-GPU work fixed, no data-path collective for the
 elementwise kernels).  The arrays (3 x 268 MB per GPU) are 6.4x the 126 MB L2, so consecutive
 kernels cannot be served from cache; that is the `l2` statement in `config`.
 
@@ -212,9 +214,27 @@ def main():
     pa, pb, pc = a.data_ptr(), b.data_ptr(), c.data_ptr()
 
     pending = [None]
+    # multi-GPU dot: fused peer-memory all-reduce inside the dot kernel; NCCL only as the fallback
+    boxes = boxes_e2e = None
+    if dist is not None and os.environ.get("BABELSTREAM_B200_BENCH_COMBINE", "p2p") == "p2p":
+        from babelstream_b200.group import connect_mailboxes
+        boxes = connect_mailboxes(dist, rank, world)
+        boxes_e2e = connect_mailboxes(dist, rank, world) if boxes is not None else None
+        if boxes_e2e is None and boxes is not None:
+            boxes.close()
+            boxes = None
+        if boxes is None and rank == 0:
+            print("bench.py: peer mailboxes unavailable (" + connect_mailboxes.last_error + "): dot falls back to NCCL",
+                  file=sys.stderr)
+    combine = "none" if dist is None else ("p2p" if boxes is not None else "nccl")
+    dot_seq = [0]
 
     def enqueue(kernel):
-        if kernel == "dot":
+        if kernel == "dot" and combine == "p2p":
+            dot_seq[0] += 1   # same count on every rank
+            bs.launch_dot_allreduce_p2p(pa, pb, n, eb, ws.data_ptr(), dot_out.data_ptr(), world=world, rank=rank,
+                                        seq=dot_seq[0], mailboxes=boxes.ptrs, stream=st)
+        elif kernel == "dot":
             if pending[0] is not None:
                 pending[0].wait()      # the previous step's all-reduce still owns dot_out
             bs.launch_dot(pa, pb, n, eb, ws.data_ptr(), dot_out.data_ptr(), stream=st)
@@ -271,12 +291,14 @@ def main():
     torch.cuda.empty_cache()
     s = bs.B200Stream(n, device=local, dtype=np.float64, ngpus=1)
     e2e_dot = torch.zeros(1, dtype=torch.float64, device="cuda")
+    if combine == "p2p":
+        s.join_group(world, rank, boxes_e2e.ptrs)   # dot() now returns the all-rank sum, one launch, no NCCL
 
     def e2e_step():
         for k in KERNEL_ORDER:
             if k == "dot":
                 v = s.dot()                       # device -> host: the sum, every step
-                if dist is not None:
+                if combine == "nccl":
                     e2e_dot.fill_(float(v))
                     dist.all_reduce(e2e_dot)
                     v = e2e_dot.item()
@@ -299,6 +321,10 @@ def main():
     # cheap sanity on the e2e arrays: every element equal (the inputs are constants), finite
     sane = bool(np.isfinite(ga[0]) and (ga == ga[0]).all() and (gb == gb[0]).all() and (gc == gc[0]).all())
     s.close()
+    if boxes is not None:
+        barrier()
+        boxes.close()
+        boxes_e2e.close()
 
     # ---- max over ranks ---------------------------------------------------------------------------
     t = torch.tensor([total_ms, e2e_s * 1e3] + [statistics.fmean(per_kernel_ms[k]) for k in KERNEL_ORDER],
@@ -332,7 +358,12 @@ def main():
                    "elements_per_gpu": n, "elements_total": n * world, "kernels": KERNEL_ORDER,
                    "bytes_per_step_per_gpu": step_bytes,
                    "l2": f"inputs larger than L2: 3 arrays x {n * eb / 1e6:.0f} MB per GPU vs 126 MB L2, no flush needed",
-                   "parallelism": f"{world} rank(s), contiguous shards, dot combined by one NCCL all-reduce of 1 element per step, overlapped with the following kernels" if world > 1 else "1 GPU",
+                   "parallelism": (f"{world} ranks (one process per GPU), contiguous shards, no collective for the elementwise kernels; "
+                                   + ("dot: partials all-reduced inside the dot kernel over NVLink peer memory (CUDA IPC mailboxes), one launch, no NCCL"
+                                      if combine == "p2p" else
+                                      "dot: one NCCL all-reduce of 1 element per step, overlapped with the following kernels"))
+                                  if world > 1 else "1 GPU",
+                   "dot_combine": combine,
                    "timing": "CUDA events on the launching stream, max over ranks"},
         "kernels_gbs": kernels,
         "kernels_frac_of_peak": {k: round(v / (world * peak), 4) for k, v in kernels.items()},

@@ -138,6 +138,40 @@ int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int el
                                   unsigned long long seq, void* const* mailboxes, const b200_launch_cfg* cfg,
                                   void* stream);
 
+/* Completion doorbell: lets a BLOCKING caller learn that a kernel has finished without
+ * cudaStreamSynchronize.  Every block takes a ticket once its stores are fenced; the block that takes
+ * the last one stores `seq` (release, system scope) to a word of mapped pinned host memory, which the
+ * caller spins on.  Whatever is enqueued next on the stream is still ordered after the whole kernel.
+ * `ticket` is one zero-initialised device word per stream (left zero; dot ignores it and uses the
+ * ticket in its workspace), `seq` must be non-zero and differ from the flag's current value.
+ * This is what LEVEL 2 does for dot (always: -1.3..1.9 us per call, the host no longer waits for the
+ * end-of-kernel flush of dot's result write) and, under option sync=doorbell, for every kernel (not the
+ * default: an elementwise kernel gains 0.2 us at best and pays 1-3 us for ~1000 same-address tickets). */
+typedef struct b200_doorbell {
+  void* ticket;
+  void* flag_host_mapped;
+  unsigned long long seq;
+} b200_doorbell;
+/* `kernel` is one of B200_COPY/MUL/ADD/TRIAD/NSTREAM/INIT; a, b, c as in the launchers above (unused
+ * ones may be NULL); s0 is the scalar (mul/triad/nstream) or init_a, s1/s2 are init_b/init_c. n > 0. */
+int b200_launch_doorbell(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1,
+                         double s2, const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream);
+int b200_launch_dot_doorbell(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
+                             void* result_host_mapped, const b200_launch_cfg* cfg, const b200_doorbell* bell,
+                             void* stream);
+
+/* Peer memory across PROCESSES (one process per GPU, e.g. under torchrun / mpirun): every rank creates
+ * its mailbox, exports it, exchanges the 64-byte handles by whatever means it has (torch.distributed,
+ * MPI, a file), opens its peers' handles and passes the resulting pointers -- its own mailbox at index
+ * `rank` -- to b200_launch_dot_allreduce_p2p or b200_join_group.  Thin wrappers of cudaMalloc and
+ * cudaIpc{GetMemHandle,OpenMemHandle,CloseMemHandle}; the GPUs must have peer access. */
+#define B200_IPC_HANDLE_BYTES 64
+int b200_dot_mailbox_create(void** mailbox);   /* on the current device, zeroed */
+int b200_dot_mailbox_destroy(void* mailbox);
+int b200_ipc_export(void* dev_ptr, void* handle_out /* B200_IPC_HANDLE_BYTES */);
+int b200_ipc_open(const void* handle, void** dev_ptr);
+int b200_ipc_close(void* dev_ptr);
+
 /* ------------------------------------------------------------------------------------------
  * LEVEL 2 -- the Stream<T> object: three device-resident arrays of n elements, sharded
  * contiguously over `ngpus` devices first_device .. first_device+ngpus-1, blocking calls
@@ -151,11 +185,20 @@ typedef struct b200_ctx b200_ctx;
 b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int* status);
 void b200_destroy(b200_ctx* ctx);
 
+/* One process per GPU: makes a single-GPU context rank `rank` of a group of `world` contexts living in
+ * other processes, each holding its own contiguous shard.  From then on b200_dot returns the sum over
+ * ALL ranks, computed by the fused peer-memory all-reduce inside the dot kernel (no NCCL, no extra
+ * launch); every rank must call b200_dot the same number of times.  mailboxes[g] is rank g's mailbox as
+ * mapped into this process (see b200_ipc_open); the array is copied.  world = 1 leaves the group. */
+int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes);
+
 /* "key=value" tuning / behaviour options, also read from the environment at create time as
  * BABELSTREAM_B200_<KEY>.  Keys: contract=fast|off, copy_variant=auto|ldst|bulk|tma,
  * dot_variant=auto|two_pass|ticket, dot_combine=auto|p2p|nccl|host (multi-GPU dot: fused peer-memory
  * all-reduce inside the dot kernel | one ncclAllReduce | rank-order sum on the host; auto = p2p when
- * every pair of GPUs has peer access, else nccl), timing=0|1, sync=stream|spin,
+ * every pair of GPUs has peer access, else nccl), timing=0|1,
+ * sync=auto|stream|spin|doorbell (how a blocking call waits: cudaStreamSynchronize | cudaStreamQuery loop |
+ * the kernel rings a host flag, see b200_doorbell; auto = doorbell for dot, cudaStreamSynchronize for the rest),
  * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk) */
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
 int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */

@@ -303,3 +303,66 @@ def test_full_size_properties(dtype):
     bs.launch_dot(a_abs.data_ptr(), ones.data_ptr(), n, eb, ws.data_ptr(), out.data_ptr(), stream=st)
     want = a_abs.double().sum().item()
     assert abs(out.item() - want) <= 64 * np.finfo(dtype).eps * want
+
+
+def _spin_until(flag_np, seq, seconds=5.0):
+    import time
+    t0 = time.perf_counter()
+    while int(flag_np[0]) != seq:
+        if time.perf_counter() - t0 > seconds:
+            return False
+    return True
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_doorbell_rings_after_the_results_are_complete(orc, dtype):
+    """LEVEL 1 doorbell (b200_doorbell): the last block to finish stores seq to mapped pinned host memory.
+    The host waits on that word ONLY (no synchronize before reading the flag); results stay bit-exact,
+    the ticket returns to zero, and consecutive launches with increasing seq ring in order."""
+    flag = torch.zeros(1, dtype=torch.int64).pin_memory()   # cudaHostAlloc: device-visible under UVA
+    flag_np = flag.numpy()
+    ticket = torch.zeros(64, dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    seq = 0
+    for n in (1, 33, 4097, (1 << 20) + 3, (1 << 23) + 5):
+        a0, b0, c0 = rand(n, dtype, 1), rand(n, dtype, 2), rand(n, dtype, 3)
+        for kern in EW + ["init"]:
+            a, b, c = a0.copy(), b0.copy(), c0.copy()
+            oracle_apply(orc, kern, a, b, c, True)
+            da, db, dc = (torch.from_numpy(x).cuda() for x in (a0, b0, c0))
+            torch.cuda.synchronize()
+            seq += 1
+            bell = bs.Doorbell(ticket.data_ptr(), flag.data_ptr(), seq)
+            bs.launch_doorbell(kern, da.data_ptr(), db.data_ptr(), dc.data_ptr(), n, a0.itemsize, bell, stream=st)
+            assert _spin_until(flag_np, seq), (kern, n, "doorbell never rang")
+            torch.cuda.synchronize()
+            for got, want in ((da, a), (db, b), (dc, c)):
+                assert same_bits(got.cpu().numpy(), want), (kern, n)
+            assert int(ticket[0].item()) == 0
+    # dot: the ring follows the result into host memory
+    res = torch.zeros(2, dtype=tdtype(dtype)).pin_memory()
+    ws = torch.zeros(bs.dot_workspace_bytes(), dtype=torch.uint8, device="cuda")
+    n = (1 << 21) + 7
+    a0, b0 = np.abs(rand(n, dtype, 5)), np.abs(rand(n, dtype, 6))
+    da, db = torch.from_numpy(a0).cuda(), torch.from_numpy(b0).cuda()
+    out = torch.zeros(1, dtype=tdtype(dtype), device="cuda")
+    torch.cuda.synchronize()
+    for variant in ("ticket", "two_pass"):
+        seq += 1
+        res.zero_()
+        bell = bs.Doorbell(None, flag.data_ptr(), seq)
+        bs.launch_dot_doorbell(da.data_ptr(), db.data_ptr(), n, a0.itemsize, ws.data_ptr(), out.data_ptr(), bell,
+                               result_host_mapped=res.data_ptr(), cfg=bs.LaunchCfg.make(variant=variant), stream=st)
+        assert _spin_until(flag_np, seq), "dot doorbell never rang"
+        got = float(res.numpy()[0])        # read BEFORE any synchronize: release/acquire through the flag
+        torch.cuda.synchronize()
+        assert got == float(out.item())
+        want = float(np.dot(a0.astype(np.float64), b0.astype(np.float64)))
+        assert abs(got - want) <= 64 * np.finfo(dtype).eps * want
+    # argument checks
+    with pytest.raises(bs.B200Error):
+        bs.launch_doorbell("copy", da.data_ptr(), 0, db.data_ptr(), n, a0.itemsize, bs.Doorbell(None, flag.data_ptr(), 1), stream=st)
+    with pytest.raises(bs.B200Error):
+        bs.launch_doorbell("copy", da.data_ptr(), 0, db.data_ptr(), n, a0.itemsize, bs.Doorbell(ticket.data_ptr(), flag.data_ptr(), 0), stream=st)
+    with pytest.raises(bs.B200Error):
+        bs.launch_doorbell("copy", da.data_ptr(), 0, db.data_ptr(), 0, a0.itemsize, bs.Doorbell(ticket.data_ptr(), flag.data_ptr(), 9), stream=st)

@@ -126,7 +126,8 @@ def test_options_and_variants(orc):
     n = 1 << 20
     ref = None
     for opts in ({}, {"copy_variant": "bulk"}, {"copy_variant": "tma"}, {"dot_variant": "two_pass"},
-                 {"sync": "spin"}, {"timing": "1"}, {"tune": "all:vec=16,unroll=4,hint=3,grid=-4;dot:vec=32,unroll=2,block=256"}):
+                 {"sync": "spin"}, {"sync": "stream"}, {"sync": "doorbell"}, {"sync": "doorbell", "dot_variant": "two_pass"},
+                 {"timing": "1"}, {"timing": "1", "sync": "doorbell"}, {"tune": "all:vec=16,unroll=4,hint=3,grid=-4;dot:vec=32,unroll=2,block=256"}):
         with bs.B200Stream(n, dtype=np.float64, **opts) as s:
             total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)
             a, b, c = s.get_arrays()
@@ -139,6 +140,26 @@ def test_options_and_variants(orc):
             else:
                 assert s.last_kernel_ms() < 0
             assert "triad" in s.describe()
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_wait_modes_bit_exact_at_every_size_class(orc, dtype):
+    """sync=auto rings a doorbell for dot and uses cudaStreamSynchronize for the elementwise kernels;
+    forcing either mode for every kernel at any size must give the same bits (and the same dot)."""
+    u = np.uint64 if dtype is np.float64 else np.uint32
+    for n in (1, 1000, (1 << 20) + 3, (1 << 24) + 9):
+        ref = None
+        for sync in ("auto", "stream", "doorbell", "spin"):
+            with bs.B200Stream(n, dtype=dtype, sync=sync) as s:
+                assert "wait:" in s.describe()
+                total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 5)
+                a, b, c = s.get_arrays()
+                g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, 5, n)
+                for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+                    assert (arr.view(u) == np.asarray(gold).view(u)).all(), (n, sync)
+                cur = total.tobytes()
+                ref = ref or cur
+                assert cur == ref, (n, sync)
 
 
 def test_constructor_errors():
@@ -265,3 +286,22 @@ def test_driver_multi_gpu():
                     env={"BABELSTREAM_B200_NGPUS": "2", "BABELSTREAM_B200_DOT_COMBINE": combine})
         assert p.returncode == 0, p.stdout + p.stderr
         assert "GPUs: 2" in p.stdout
+
+
+GROUP_WORKER = os.path.join(ROOT, "tests", "group_worker.py")
+
+
+@multi
+@pytest.mark.parametrize("world", [2, 8])
+def test_process_group_fused_dot_allreduce(world):
+    """One process per GPU (the bench.py / torchrun layout): mailboxes exchanged as CUDA IPC handles,
+    b200_join_group, then every rank's dot() is the all-rank sum from the fused peer-memory all-reduce:
+    identical bits on all ranks, equal to the rank-order sum of the per-rank partials."""
+    import sys
+    world = min(world, bs.device_count())
+    port = 29600 + world
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), GROUP_WORKER],
+                       capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
+    assert f"group ok world={world}" in p.stdout, p.stdout[-3000:]

@@ -66,6 +66,36 @@ if has overhead; then
     BABELSTREAM_B200_SYNC=spin BABELSTREAM_B200_HOSTPROF=1 ./build/b200-stream --csv -s 1024 -n 3000 2>&1 | grep -E "^(Copy|Triad|Dot),|hostprof" | cut -d, -f1,6,8
   done
 fi
+if has waitmodes; then
+  # blocking-call latency: cudaStreamSynchronize vs the kernel-rung doorbell, against the reference, driver-timed
+  for s in 1024 1048576 4194304 33554432; do
+    for rep in 1 2; do
+      ./oracle/_ref/cuda-stream --csv --gigabytes -s $s --only All -n 300 2>/dev/null | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,6 | tr '\n' ' ' | sed "s/^/s=$s ref_cuda        : /"; echo
+      for m in stream doorbell auto; do
+        BABELSTREAM_B200_SYNC=$m ./build/b200-stream --csv --gigabytes -s $s --only All -n 300 2>/dev/null | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,6 | tr '\n' ' ' | sed "s/^/s=$s b200 $m : /"; echo
+      done
+    done
+  done
+fi
+if has smallncu; then
+  # device-side durations at an L2-resident size: the reference's kernels vs ours
+  ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/small_ref.csv ./oracle/_ref/cuda-stream -s 1048576 -n 6 --only All > /dev/null 2>&1
+  BABELSTREAM_B200_SYNC=stream ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/small_b200.csv ./build/b200-stream -s 1048576 -n 6 --only All > /dev/null 2>&1
+  BABELSTREAM_B200_SYNC=doorbell ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/small_b200_bell.csv ./build/b200-stream -s 1048576 -n 6 --only All > /dev/null 2>&1
+  python - <<'PY'
+import csv, collections
+for f in ("small_ref", "small_b200", "small_b200_bell"):
+    d = collections.defaultdict(list)
+    try:
+        rows = list(csv.reader(l for l in open(f"gpurun_out/{f}.csv") if l.startswith('"')))
+    except Exception as e:
+        print(f, "unreadable", e); continue
+    hdr = rows[0]; ki = hdr.index("Kernel Name"); vi = hdr.index("Metric Value")
+    for r in rows[1:]:
+        d[r[ki][:60]].append(float(r[vi].replace(",", "")))
+    print(f, {k: round(sorted(v)[len(v)//2]) for k, v in d.items()})
+PY
+fi
 if has driver; then
   for s in 33554432 536870912; do
     for rep in 1 2; do
