@@ -28,7 +28,7 @@ SRCS := $(wildcard $(CSRC)/*.cu)
 OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(SRCS))
 HDRS := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) include/b200_stream.h
 
-.PHONY: all lib driver oracle clean ptxas
+.PHONY: all lib driver oracle clean ptxas probe
 all: lib oracle driver
 
 lib: $(LIB)
@@ -68,6 +68,12 @@ else
 driver:
 	@echo "Makefile: $(BABELSTREAM_ROOT)/src/main.cpp not present -- b200-stream not rebuilt"
 endif
+
+# tools/latency_probe: host-clock split of a tiny blocking call (bare kernel vs LEVEL 1 vs LEVEL 2)
+probe: build/latency_probe
+build/latency_probe: tools/latency_probe.cu $(LIB) include/b200_stream.h
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -ccbin $(HOSTCXX) -Iinclude $< -o $@ \
+	    -L$(CSRC) -lb200stream -Xlinker -rpath,'$$ORIGIN/../$(CSRC)'
 
 ptxas:
 	@cat $(OBJDIR)/*.ptxas.log | grep -E "Compiling|registers|spill" | paste - - - | sort | uniq | head -2000

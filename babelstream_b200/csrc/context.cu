@@ -69,7 +69,7 @@ struct NcclApi {
   }
 };
 
-enum { CMD_NONE = 0, CMD_KERNEL, CMD_READ, CMD_WRITE, CMD_QUIT };
+enum { CMD_NONE = 0, CMD_KERNEL, CMD_READ, CMD_WRITE, CMD_PREFETCH, CMD_QUIT };
 enum { COMBINE_AUTO = -1, COMBINE_NCCL = 0, COMBINE_HOST = 1, COMBINE_P2P = 2 };
 enum { SYNC_AUTO = -1, SYNC_STREAM = 0, SYNC_SPIN = 1, SYNC_DOORBELL = 2 };
 
@@ -100,6 +100,7 @@ struct Command {
   double s0 = 0, s1 = 0, s2 = 0;
   unsigned long long seq = 0;                   // dot: sequence number of the p2p all-reduce
   void* host[3] = {nullptr, nullptr, nullptr};  // read: destinations; write: sources
+  int prefetch_to = 0;                          // CMD_PREFETCH: 0 = the shard's GPU, 1 = the CPU
 };
 
 }  // namespace b200
@@ -115,6 +116,7 @@ struct b200_ctx {
   // options
   b200_launch_cfg tune[B200_NUM_KERNELS];
   bool timing = false;
+  bool created = false;  // b200_create finished: the allocation-time options are frozen
   int sync_mode = SYNC_AUTO;
   // one process per GPU (b200_join_group): this context is rank group_rank of group_world
   int group_world = 1, group_rank = 0;
@@ -125,6 +127,13 @@ struct b200_ctx {
   bool p2p_ready = false;
   void* mailboxes[kMaxPeers] = {};
   unsigned long long dot_seq = 0;
+
+  // mem=managed: the reference's MEM=MANAGED build (src/cuda/model.cmake:6-10, CUDAStream.cu:37-38,217-221).
+  // One cudaMallocManaged range per array; every shard is a sub-range whose preferred location is its
+  // GPU.  get_arrays hands out the ranges themselves (no gather, no second copy of the data).
+  bool managed = false;
+  void* managed_base[3] = {nullptr, nullptr, nullptr};
+  bool managed_on_host = false;  // get_arrays moved the pages to the CPU; move them back before the next kernel
 
   // host mirrors for get_arrays
   void* host[3] = {nullptr, nullptr, nullptr};
@@ -272,9 +281,17 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
     for (int k = 0; k < 3; k++) {
       if (!cmd.host[k] || s->count == 0) continue;
       char* h = static_cast<char*>(cmd.host[k]) + s->begin * eb;
-      if (cmd.kind == CMD_READ) B200_CUDA(cudaMemcpyAsync(h, dev[k], s->count * eb, cudaMemcpyDeviceToHost, s->stream));
-      else B200_CUDA(cudaMemcpyAsync(dev[k], h, s->count * eb, cudaMemcpyHostToDevice, s->stream));
+      // cudaMemcpyDefault: the device side is a managed range under mem=managed
+      if (cmd.kind == CMD_READ) B200_CUDA(cudaMemcpyAsync(h, dev[k], s->count * eb, cudaMemcpyDefault, s->stream));
+      else B200_CUDA(cudaMemcpyAsync(dev[k], h, s->count * eb, cudaMemcpyDefault, s->stream));
     }
+    B200_CUDA(cudaStreamSynchronize(s->stream));
+    return B200_OK;
+  }
+  if (cmd.kind == CMD_PREFETCH) {
+    void* dev[3] = {s->a, s->b, s->c};
+    const int dst = cmd.prefetch_to ? cudaCpuDeviceId : s->dev;
+    for (int k = 0; k < 3 && s->count; k++) B200_CUDA(cudaMemPrefetchAsync(dev[k], s->count * eb, dst, s->stream));
     B200_CUDA(cudaStreamSynchronize(s->stream));
     return B200_OK;
   }
@@ -364,6 +381,14 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
     ctx->combine = val == "host" ? COMBINE_HOST : val == "p2p" ? COMBINE_P2P : val == "nccl" ? COMBINE_NCCL : COMBINE_AUTO;
   } else if (key == "timing") {
     ctx->timing = (val == "1" || val == "on" || val == "true");
+  } else if (key == "mem") {
+    const bool want = val == "managed";
+    if (!want && val != "device" && val != "default") { set_error("mem must be device or managed, got '%s'", val.c_str()); return B200_EINVAL; }
+    if (ctx->created && want != ctx->managed) {
+      set_error("mem is fixed when the arrays are allocated: pass it to b200_create_opts or set BABELSTREAM_B200_MEM");
+      return B200_EINVAL;
+    }
+    ctx->managed = want;
   } else if (key == "sync") {
     ctx->sync_mode = val == "spin" ? SYNC_SPIN : val == "stream" ? SYNC_STREAM : val == "doorbell" ? SYNC_DOORBELL : SYNC_AUTO;
   } else if (key == "tune") {
@@ -503,16 +528,22 @@ void b200_destroy(b200_ctx* ctx) {
     if (s->stream) cudaStreamDestroy(s->stream);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
-    cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox); cudaFree(s->bell_ticket);
+    if (!ctx->managed) { cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); }
+    cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox); cudaFree(s->bell_ticket);
     if (s->dot_host) cudaFreeHost(s->dot_host);
     delete s;
   }
+  for (void* p : ctx->managed_base) if (p) cudaFree(p);
   free_host_mirrors(ctx);
   if (!ctx->shards.empty()) cudaSetDevice(ctx->first_device);
   delete ctx;
 }
 
 b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int* status) {
+  return b200_create_opts(first_device, ngpus, n, elem_bytes, nullptr, status);
+}
+
+b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes, const char* const* options, int* status) {
   int rc = B200_OK;
   b200_ctx* ctx = nullptr;
   auto fail = [&](int code) -> b200_ctx* {
@@ -540,11 +571,33 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
   memset(ctx->tune, 0, sizeof ctx->tune);
 
   // options from the environment: BABELSTREAM_B200_<KEY>
-  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune"};
+  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem"};
   for (const char* k : keys) {
     std::string env = "BABELSTREAM_B200_";
     for (const char* p = k; *p; p++) env += (char)toupper(*p);
     if (const char* v = getenv(env.c_str())) { rc = apply_option(ctx, k, v); if (rc) return fail(rc); }
+  }
+  // explicit options override the environment
+  for (const char* const* o = options; o && *o; o++) {
+    const std::string kv = *o;
+    const size_t eq = kv.find('=');
+    if (eq == std::string::npos) { set_error("option '%s' is not key=value", *o); return fail(B200_EINVAL); }
+    rc = apply_option(ctx, kv.substr(0, eq), kv.substr(eq + 1));
+    if (rc) return fail(rc);
+  }
+  ctx->created = false;
+
+  // mem=managed: the three arrays are single managed ranges; shard boundaries move to 2 MiB multiples
+  // (the managed page size) so that no page is shared by two GPUs
+  const size_t shard_align = (ctx->managed && ngpus > 1 && n * (size_t)elem_bytes / (size_t)ngpus >= (8u << 20)) ? (2u << 20) : 128;
+  if (ctx->managed) {
+    int dev0_managed = 0;
+    cudaDeviceGetAttribute(&dev0_managed, cudaDevAttrConcurrentManagedAccess, first_device);
+    if (!dev0_managed) { set_error("mem=managed needs concurrent managed access, which device %d does not offer", first_device); return fail(B200_EUNSUPPORTED); }
+    cudaError_t e = cudaSetDevice(first_device);
+    const size_t array_bytes = n ? n * (size_t)elem_bytes : 256;
+    for (int k = 0; k < 3 && e == cudaSuccess; k++) e = cudaMallocManaged(&ctx->managed_base[k], array_bytes);
+    if (e != cudaSuccess) return fail(cuda_fail(e, "cudaMallocManaged", __FILE__, __LINE__));
   }
 
   if (const char* hp = getenv("BABELSTREAM_B200_HOSTPROF")) ctx->hostprof = atoi(hp) != 0;
@@ -555,7 +608,7 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
     ctx->shards.push_back(s);
     s->dev = first_device + g;
     s->rank = g;
-    b200_shard_range(n, elem_bytes, ngpus, g, &s->begin, &s->count);
+    shard_range_aligned(n, elem_bytes, ngpus, g, shard_align, &s->begin, &s->count);
     auto cu = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && rc == B200_OK) rc = cuda_fail(e, what, __FILE__, __LINE__); };
     cu(cudaSetDevice(s->dev), "cudaSetDevice");
     if (rc) return fail(rc);
@@ -575,9 +628,19 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
     cu(cudaEventCreate(&s->ev0), "cudaEventCreate");
     cu(cudaEventCreate(&s->ev1), "cudaEventCreate");
     const size_t alloc = shard_bytes ? shard_bytes : 256;
-    cu(cudaMalloc(&s->a, alloc), "cudaMalloc(a)");
-    cu(cudaMalloc(&s->b, alloc), "cudaMalloc(b)");
-    cu(cudaMalloc(&s->c, alloc), "cudaMalloc(c)");
+    if (ctx->managed) {
+      void** mine[3] = {&s->a, &s->b, &s->c};
+      for (int k = 0; k < 3; k++) {
+        *mine[k] = static_cast<char*>(ctx->managed_base[k]) + s->begin * (size_t)elem_bytes;
+        if (!shard_bytes) continue;
+        cu(cudaMemAdvise(*mine[k], shard_bytes, cudaMemAdviseSetPreferredLocation, s->dev), "cudaMemAdvise(preferred location)");
+        cu(cudaMemPrefetchAsync(*mine[k], shard_bytes, s->dev, s->stream), "cudaMemPrefetchAsync");
+      }
+    } else {
+      cu(cudaMalloc(&s->a, alloc), "cudaMalloc(a)");
+      cu(cudaMalloc(&s->b, alloc), "cudaMalloc(b)");
+      cu(cudaMalloc(&s->c, alloc), "cudaMalloc(c)");
+    }
     cu(cudaMalloc(&s->dot_ws, kDotWorkspaceBytes), "cudaMalloc(dot workspace)");
     cu(cudaMalloc(&s->dot_dev, 16), "cudaMalloc(dot scalars)");
     cu(cudaMalloc(&s->bell_ticket, 256), "cudaMalloc(doorbell ticket)");
@@ -598,6 +661,7 @@ b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int
     for (int g = 0; g < ngpus; g++) ctx->workers.emplace_back(worker_main, ctx, g);
   }
   cudaSetDevice(first_device);
+  ctx->created = true;
   if (status) *status = B200_OK;
   return ctx;
 }
@@ -634,6 +698,7 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
   snprintf(line, sizeof line, "GPUs: %d (devices %d..%d), %zu elements of %d bytes, shard %zu elements\n", ctx->ngpus,
            ctx->first_device, ctx->first_device + ctx->ngpus - 1, ctx->n, ctx->elem_bytes, ctx->shards[0]->count);
   out += line;
+  if (ctx->managed) out += "  memory: MANAGED (one cudaMallocManaged range per array, preferred location = owning GPU, prefetched; get_arrays returns the ranges)\n";
   const char* names[B200_NUM_KERNELS] = {"copy", "mul", "add", "triad", "nstream", "dot", "init"};
   for (int k = 0; k < B200_NUM_KERNELS; k++) {
     Resolved r;
@@ -666,8 +731,20 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
   return B200_OK;
 }
 
+// mem=managed: after get_arrays the pages live in host memory; bring every shard home before it is used
+// on the GPU again (the kernels would fault them over one by one otherwise)
+static int managed_home(b200_ctx* ctx) {
+  if (!ctx->managed_on_host) return B200_OK;
+  Command cmd;
+  cmd.kind = CMD_PREFETCH; cmd.prefetch_to = 0;
+  if (int rc = run_all(ctx, cmd)) return rc;
+  ctx->managed_on_host = false;
+  return B200_OK;
+}
+
 static int run_kernel(b200_ctx* ctx, int kernel, double s0, double s1, double s2) {
   if (!ctx) { set_error("null context"); return B200_EINVAL; }
+  if (int rc = managed_home(ctx)) return rc;
   Command cmd;
   cmd.kind = CMD_KERNEL; cmd.kernel = kernel; cmd.s0 = s0; cmd.s1 = s1; cmd.s2 = s2;
   if (kernel == B200_DOT) cmd.seq = ++ctx->dot_seq;
@@ -723,6 +800,20 @@ int b200_write_arrays(b200_ctx* ctx, const void* a, const void* b, const void* c
 
 int b200_get_arrays(b200_ctx* ctx, const void** a, const void** b, const void** c) {
   if (!ctx) { set_error("null context"); return B200_EINVAL; }
+  if (ctx->managed) {
+    // "Unified memory: return pointers to device memory" (CUDAStream.cu:217-221) -- after moving the pages
+    // to the CPU in bulk, all shards in parallel, so that check_solution does not fault them over one by one
+    if (!ctx->managed_on_host) {
+      Command cmd;
+      cmd.kind = CMD_PREFETCH; cmd.prefetch_to = 1;
+      if (int rc = run_all(ctx, cmd)) return rc;
+      ctx->managed_on_host = true;
+    }
+    if (a) *a = ctx->managed_base[0];
+    if (b) *b = ctx->managed_base[1];
+    if (c) *c = ctx->managed_base[2];
+    return B200_OK;
+  }
   if (int rc = ensure_host_mirrors(ctx)) return rc;
   if (int rc = transfer(ctx, CMD_READ, ctx->host[0], ctx->host[1], ctx->host[2])) return rc;
   if (a) *a = ctx->host[0];

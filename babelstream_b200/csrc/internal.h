@@ -42,6 +42,10 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
 // grid size for `ntiles` tiles under the policy
 unsigned grid_for(int grid_policy, unsigned long long ntiles, int num_sms);
 
+// Contiguous shard g of ngpus with boundaries on multiples of align_bytes (128 for device memory,
+// b200_shard_range; 2 MiB for managed memory so that no page has two owners)
+void shard_range_aligned(size_t n, int elem_bytes, int ngpus, int g, size_t align_bytes, size_t* begin, size_t* count);
+
 // Geometry of one vectorised pass over n elements whose (up to three) base pointers are p0..p2
 // (null = unused).  Falls back to scalar accesses when the pointers are not mutually congruent
 // modulo vec_bytes.

@@ -182,6 +182,19 @@ Geometry make_geometry(const void* p0, const void* p1, const void* p2, size_t n,
   return g;
 }
 
+void shard_range_aligned(size_t n, int elem_bytes, int ngpus, int g, size_t align_bytes, size_t* begin, size_t* count) {
+  // ceil split rounded up to a multiple of align_bytes; trailing shards may be short or empty
+  const size_t align = align_bytes / (size_t)elem_bytes;
+  size_t per = (n + (size_t)ngpus - 1) / (size_t)ngpus;
+  per = (per + align - 1) / align * align;
+  size_t b = per * (size_t)g;
+  if (b > n) b = n;
+  size_t e = b + per;
+  if (e > n) e = n;
+  *begin = b;
+  *count = e - b;
+}
+
 }  // namespace b200
 
 // ---- exported host logic --------------------------------------------------------------------
@@ -194,16 +207,7 @@ int b200_shard_range(size_t n, int elem_bytes, int ngpus, int g, size_t* begin, 
     b200::set_error("b200_shard_range: bad arguments (n=%zu elem_bytes=%d ngpus=%d g=%d)", n, elem_bytes, ngpus, g);
     return B200_EINVAL;
   }
-  // ceil split rounded up to a multiple of 128 bytes; trailing shards may be short or empty
-  const size_t align = 128 / (size_t)elem_bytes;
-  size_t per = (n + (size_t)ngpus - 1) / (size_t)ngpus;
-  per = (per + align - 1) / align * align;
-  size_t b = per * (size_t)g;
-  if (b > n) b = n;
-  size_t e = b + per;
-  if (e > n) e = n;
-  *begin = b;
-  *count = e - b;
+  b200::shard_range_aligned(n, elem_bytes, ngpus, g, 128, begin, count);
   return B200_OK;
 }
 

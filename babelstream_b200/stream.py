@@ -115,6 +115,7 @@ def lib() -> C.CDLL:
         "b200_ipc_close": (ci, [vp]),
         "b200_join_group": (ci, [vp, ci, ci, C.POINTER(vp)]),
         "b200_create": (vp, [ci, ci, sz, ci, C.POINTER(ci)]),
+        "b200_create_opts": (vp, [ci, ci, sz, ci, C.POINTER(cp), C.POINTER(ci)]),
         "b200_destroy": (None, [vp]),
         "b200_set_option": (ci, [vp, cp, cp]),
         "b200_describe": (ci, [vp, cp, ci]),
@@ -296,11 +297,12 @@ class B200Stream:
         if self.array_size <= 0:
             raise B200Error(-1, "Invalid array size.")  # src/main.cpp:462-466
         st = C.c_int(0)
-        self._h = lib().b200_create(device, ngpus, self.array_size, self.elem_bytes, C.byref(st))
+        # options are applied before the arrays are allocated (mem=managed needs that)
+        opts = [f"{k}={v}".encode() for k, v in options.items()]
+        arr = (C.c_char_p * (len(opts) + 1))(*opts, None)
+        self._h = lib().b200_create_opts(device, ngpus, self.array_size, self.elem_bytes, arr, C.byref(st))
         if not self._h:
             raise B200Error(st.value, lib().b200_last_error().decode(errors="replace"))
-        for k, v in options.items():
-            self.set_option(k, v)
         self.init_arrays(*init)
 
     # -- lifetime ----------------------------------------------------------------------------

@@ -162,6 +162,38 @@ def test_wait_modes_bit_exact_at_every_size_class(orc, dtype):
                 assert cur == ref, (n, sync)
 
 
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_managed_memory_mode(orc, dtype):
+    """mem=managed (the reference's MEM=MANAGED build, src/cuda/model.cmake:6-10): same bits; get_arrays
+    returns the managed ranges themselves (CUDAStream.cu:217-221) and the kernels keep working afterwards."""
+    u = np.uint64 if dtype is np.float64 else np.uint32
+    for n in (1000, (1 << 22) + 17):
+        with bs.B200Stream(n, dtype=dtype, mem="managed") as s:
+            assert "MANAGED" in s.describe()
+            total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)
+            a, b, c = s.get_arrays()
+            g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, 3, n)
+            for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+                assert (arr.view(u) == np.asarray(gold).view(u)).all(), n
+            assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, total) == 0
+            a2, _, _ = s.get_arrays()
+            assert a2.ctypes.data == a.ctypes.data          # the same range, no mirror
+            # pages are on the CPU now: the next kernels bring them home and continue the recurrence
+            drive(s, orc, O.ALL, O.ORDER_CLASSIC, 2)
+            a, b, c = s.get_arrays()
+            g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, 5, n)
+            for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+                assert (arr.view(u) == np.asarray(gold).view(u)).all(), n
+            ra, rb, rc = s.read_arrays()
+            assert np.array_equal(ra.view(u), a.view(u)) and np.array_equal(rc.view(u), c.view(u))
+            with pytest.raises(bs.B200Error):
+                s.set_option("mem", "device")   # fixed at allocation time
+    with pytest.raises(bs.B200Error):
+        bs.B200Stream(16, mem="bogus")
+    with pytest.raises(bs.B200Error):
+        bs.B200Stream(16, nonsense="1")
+
+
 def test_constructor_errors():
     with pytest.raises(bs.B200Error) as e:
         bs.B200Stream(1024, device=99)
@@ -207,6 +239,13 @@ def test_driver_cli_matrix(args):
 
 
 @needs_bin
+@needs_bin
+def test_driver_managed_memory():
+    p = run_bin("-s", str((1 << 22) + 3), "-n", "10", "--only", "All", env={"BABELSTREAM_B200_MEM": "managed"})
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "MANAGED" in p.stdout
+
+
 def test_driver_csv_and_contract_off():
     p = run_bin("-s", "4194304", "-n", "20", "--csv", "--only", "All", env={"BABELSTREAM_B200_CONTRACT": "off"})
     assert p.returncode == 0, p.stdout + p.stderr
@@ -253,6 +292,26 @@ def test_multi_gpu_sharded_bit_exact(orc, dtype, combine):
                     assert t2.tobytes() == t3.tobytes()
     finally:
         os.environ.pop("BABELSTREAM_B200_DOT_COMBINE", None)
+
+
+@multi
+@pytest.mark.parametrize("combine", ["p2p", "host"])
+def test_multi_gpu_managed_memory(orc, combine):
+    """mem=managed over several GPUs: one managed range per array, shards on 2 MiB boundaries."""
+    top = min(bs.device_count(), 8)
+    for ngpus in sorted({2, top}):
+        for n in (1000, (1 << 23) + 17):
+            with bs.B200Stream(n, dtype=np.float64, ngpus=ngpus, mem="managed", dot_combine=combine) as s:
+                total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)
+                a, b, c = s.get_arrays()
+                g = orc.gold(np.float64, O.ALL, O.ORDER_CLASSIC, 3, n)
+                for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+                    assert (arr.view(np.uint64) == np.asarray(gold).view(np.uint64)).all(), (ngpus, n)
+                assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, total) == 0
+                if n > (1 << 23):
+                    info = [s.shard_info(g_) for g_ in range(ngpus)]
+                    assert all(i["begin"] * 8 % (2 << 20) == 0 for i in info)
+                    assert sum(i["count"] for i in info) == n
 
 
 @multi
