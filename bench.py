@@ -340,6 +340,15 @@ def main():
         return 0
 
     peak, peak_src = measured_peak()
+    # what the reference's cuda model prints as PEAK: 2 x memory clock x bus width (CUDAStream.cu:107-108)
+    device_peak = None
+    try:
+        import ctypes as C
+        clk, bus = C.c_int(), C.c_int()
+        if bs.lib().b200_device_info(local, None, None, None, None, None, C.byref(clk), C.byref(bus)) == 0:
+            device_peak = round(2.0 * (clk.value / 1000.0) * (bus.value / 8) / 1000.0, 1)
+    except Exception:
+        pass
     ms_per_step = total_ms / K
     value = world * step_bytes / (ms_per_step * 1e-3) / 1e9
     kernels = {k: round(world * WEIGHT[k] * eb * n / (kernel_ms[k] * 1e-3) / 1e9, 1) for k in KERNEL_ORDER}
@@ -370,7 +379,9 @@ def main():
         "peak_gbs_per_gpu": peak, "peak_source": peak_src,
         "roofline": {"bound": "hbm", "kernel": "triad (ew_kernel<double, OP_TRIAD, ...>)", "achieved": round(triad_gbs_per_gpu, 1),
                      "peak": peak, "unit": "GB/s", "frac": round(triad_gbs_per_gpu / peak, 4),
-                     "frac_of_nominal_8000": round(triad_gbs_per_gpu / 8000.0, 4), "traffic": traffic,
+                     "frac_of_nominal_8000": round(triad_gbs_per_gpu / 8000.0, 4),
+                     "frac_of_device_formula_peak": round(triad_gbs_per_gpu / device_peak, 4) if device_peak else None,
+                     "device_formula_peak": device_peak, "traffic": traffic,
                      "algorithmic_bytes_per_launch": WEIGHT["triad"] * eb * n, "avg_launch_ms": round(kernel_ms["triad"], 6),
                      "peak_source": peak_src},
         "e2e": {"value": round(world * step_bytes / (e2e_ms / K * 1e-3) / 1e9, 1), "unit": UNIT, "h2d_bytes_per_step": 0,
@@ -400,7 +411,8 @@ def main():
                     r = run_stream_binary(b200_bin, big, 30, only="Triad")
                     extras["north_star_triad_2^29"] = {"b200_stream_driver_gbs": round(r["triad"]["gbs"], 1),
                                                       "frac_of_measured_peak": round(r["triad"]["gbs"] / peak, 4),
-                                                      "frac_of_nominal_8000": round(r["triad"]["gbs"] / 8000, 4)}
+                                                      "frac_of_nominal_8000": round(r["triad"]["gbs"] / 8000, 4),
+                                                      "frac_of_device_formula_peak": round(r["triad"]["gbs"] / device_peak, 4) if device_peak else None}
                     if os.path.exists(cuda_bin):
                         r2 = run_stream_binary(cuda_bin, big, 30, only="Triad")
                         extras["north_star_triad_2^29"]["reference_cuda_stream_driver_gbs"] = round(r2["triad"]["gbs"], 1)

@@ -310,7 +310,7 @@ def test_multi_gpu_managed_memory(orc, combine):
                 assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, total) == 0
                 if n > (1 << 23):
                     info = [s.shard_info(g_) for g_ in range(ngpus)]
-                    assert all(i["begin"] * 8 % (2 << 20) == 0 for i in info)
+                    assert all(i["begin"] * 8 % (2 << 20) == 0 for i in info if i["count"])  # trailing shards may be empty
                     assert sum(i["count"] for i in info) == n
 
 

@@ -96,6 +96,26 @@ for f in ("small_ref", "small_b200", "small_b200_bell"):
     print(f, {k: round(sorted(v)[len(v)//2]) for k, v in d.items()})
 PY
 fi
+if has probe; then
+  for n in 1024 1048576; do echo "== latency probe n=$n"; ./build/latency_probe $n; done 2>&1 | tee gpurun_out/latency_probe.txt
+  BABELSTREAM_B200_HOSTPROF=1 ./build/b200-stream --csv -s 1024 -n 3000 2>&1 | grep -E "hostprof"
+fi
+if has managed; then
+  for s in 33554432 536870912; do
+    for m in device managed; do
+      BABELSTREAM_B200_MEM=$m timeout 300 ./build/b200-stream --csv --gigabytes -s $s --only All -n 50 2>&1 | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,5 | tr '\n' ' ' | sed "s/^/s=$s mem=$m : /"; echo
+    done
+  done 2>&1 | tee gpurun_out/managed_vs_device.txt
+fi
+if has ncu29; then
+  # north-star size: every kernel once, full metric set, through the unmodified driver (iteration 2 of 3)
+  ./build/b200-stream -s 536870912 --only All -n 3 > gpurun_out/plain29.log 2>&1 &&
+  ncu --set full --clock-control none --import-source on -k "regex:ew_kernel|dot_kernel" -s 7 -c 6 -f -o gpurun_out/prof_2p29 ./build/b200-stream -s 536870912 --only All -n 3 > gpurun_out/ncu29.log 2>&1
+  echo "ncu29 rc=$?"; tail -2 gpurun_out/ncu29.log
+  ncu -i gpurun_out/prof_2p29.ncu-rep --page raw --csv --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,dram__throughput.avg.pct_of_peak_sustained_elapsed,sm__warps_active.avg.pct_of_peak_sustained_active,launch__registers_per_thread,launch__grid_size,launch__block_size > gpurun_out/ncu29_summary.csv 2>&1
+  ncu --set full --clock-control none -k "regex:for_each_kernel|dot_kernel" -s 7 -c 6 -f -o gpurun_out/prof_2p29_ref ./oracle/_ref/cuda-stream -s 536870912 --only All -n 3 > gpurun_out/ncu29_ref.log 2>&1
+  ncu -i gpurun_out/prof_2p29_ref.ncu-rep --page raw --csv --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,dram__throughput.avg.pct_of_peak_sustained_elapsed,sm__warps_active.avg.pct_of_peak_sustained_active,launch__registers_per_thread,launch__grid_size,launch__block_size > gpurun_out/ncu29_ref_summary.csv 2>&1
+fi
 if has driver; then
   for s in 33554432 536870912; do
     for rep in 1 2; do

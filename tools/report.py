@@ -16,7 +16,9 @@ from collections import defaultdict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 KERNELS = ["copy", "mul", "add", "triad", "dot", "nstream"]
-NOMINAL, FORMULA = 8000.0, 8183.8
+# FORMULA: what cuda-stream itself prints on the box, "3996 MHz x 7680-bit = 7672.32 GB/s PEAK"
+# (src/cuda/CUDAStream.cu:107-108; this B200 SKU reports a 7680-bit bus, not 8192)
+NOMINAL, FORMULA = 8000.0, 7672.3
 
 
 def measured_peak():
