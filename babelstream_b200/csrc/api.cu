@@ -118,7 +118,7 @@ int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, d
 
 int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
                       void* result_host_mapped, int world, int rank, unsigned long long seq, void* const* mailboxes,
-                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream) {
+                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream, bool send_only) {
   if (int rc = check_common(n, elem_bytes)) return rc;
   if (int rc = check_bell(bell, false)) return rc;
   if (!workspace || (n > 0 && (!a || !b))) { set_error("b200_launch_dot: null pointer"); return B200_EINVAL; }
@@ -129,6 +129,7 @@ int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, vo
   call.a = a; call.b = b; call.n = n; call.elem_bytes = elem_bytes;
   call.workspace = workspace; call.result_dev = result_dev; call.result_host = result_host_mapped;
   call.p2p_world = world; call.p2p_rank = rank; call.p2p_seq = seq; call.p2p_mailboxes = mailboxes;
+  call.p2p_send_only = send_only;
   if (bell) { call.bell.flag = bell->flag_host_mapped; call.bell.seq = bell->seq; }
   call.stream = static_cast<cudaStream_t>(stream);
   call.g = make_geometry(a, b, nullptr, n, elem_bytes, call.r.vec_bytes, call.r.block, call.r.unroll, call.r.cache_hint);
@@ -243,6 +244,22 @@ int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int el
   if (world < 1 || world > kMaxPeers) { set_error("dot p2p: world must be 1..%d", kMaxPeers); return B200_EINVAL; }
   return launch_dot_common(a, b, n, elem_bytes, workspace, result_dev, result_host_mapped, world, rank, seq, mailboxes,
                            cfg, nullptr, stream);
+}
+
+int b200_launch_dot_send_p2p(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* partial_dev,
+                             int world, int rank, unsigned long long seq, void* const* mailboxes,
+                             const b200_launch_cfg* cfg, void* stream) {
+  if (world < 2 || world > kMaxPeers) { set_error("dot send: world must be 2..%d", kMaxPeers); return B200_EINVAL; }
+  return launch_dot_common(a, b, n, elem_bytes, workspace, partial_dev, nullptr, world, rank, seq, mailboxes, cfg, nullptr,
+                           stream, /*send_only=*/true);
+}
+
+int b200_launch_dot_collect_p2p(int elem_bytes, void* result_dev, void* result_host_mapped, int world, int rank,
+                                unsigned long long seq, void* const* mailboxes, void* stream) {
+  if (int rc = check_common(0, elem_bytes)) return rc;
+  if (!current_device_props(nullptr)) return B200_ENODEVICE;
+  return launch_dot_collect(elem_bytes, result_dev, result_host_mapped, world, rank, seq, mailboxes,
+                            static_cast<cudaStream_t>(stream));
 }
 
 // ---- cross-process peer memory (one process per GPU) ------------------------------------------

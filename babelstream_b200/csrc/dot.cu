@@ -25,7 +25,7 @@ static int launch_dot_typed(const DotCall& call) {
   }
   if (call.r.block > dot_block_bound(vb, u, MODE)) {
     set_error("dot: block %d too large for vec_bytes=%d unroll=%d%s (max %d)", call.r.block, vb, u,
-              MODE == DOT_TICKET_P2P ? " with the fused peer-memory all-reduce" : "", dot_block_bound(vb, u, MODE));
+              MODE >= DOT_TICKET_P2P ? " with the fused peer-memory all-reduce" : "", dot_block_bound(vb, u, MODE));
     return B200_EINVAL;
   }
   DotArgs args;
@@ -66,16 +66,36 @@ int launch_dot_impl(const DotCall& call) {
     set_error("dot grid %u exceeds the workspace capacity of %d blocks", call.grid, kDotMaxBlocks);
     return B200_EINVAL;
   }
-  const int mode = call.p2p_world > 1 ? DOT_TICKET_P2P : ticket ? DOT_TICKET : DOT_TWO_PASS;
+  const int mode = call.p2p_world > 1 ? (call.p2p_send_only ? DOT_TICKET_SEND : DOT_TICKET_P2P) : ticket ? DOT_TICKET : DOT_TWO_PASS;
 #define B200_DOT_DISPATCH(T)                                                                                   \
   switch (mode) {                                                                                              \
     case DOT_TWO_PASS: return fused ? launch_dot_typed<T, true, DOT_TWO_PASS>(call) : launch_dot_typed<T, false, DOT_TWO_PASS>(call); \
     case DOT_TICKET: return fused ? launch_dot_typed<T, true, DOT_TICKET>(call) : launch_dot_typed<T, false, DOT_TICKET>(call);       \
+    case DOT_TICKET_SEND: return fused ? launch_dot_typed<T, true, DOT_TICKET_SEND>(call) : launch_dot_typed<T, false, DOT_TICKET_SEND>(call); \
     default: return fused ? launch_dot_typed<T, true, DOT_TICKET_P2P>(call) : launch_dot_typed<T, false, DOT_TICKET_P2P>(call);     \
   }
   if (call.elem_bytes == 8) { B200_DOT_DISPATCH(double) }
   B200_DOT_DISPATCH(float)
 #undef B200_DOT_DISPATCH
+}
+
+int launch_dot_collect(int elem_bytes, void* result_dev, void* result_host, int world, int rank, unsigned long long seq,
+                       void* const* mailboxes, cudaStream_t stream) {
+  if (world < 2 || world > kMaxPeers || rank < 0 || rank >= world || !mailboxes || seq == 0) {
+    set_error("dot collect: bad world/rank/seq/mailboxes (world %d, rank %d)", world, rank);
+    return B200_EINVAL;
+  }
+  P2PArgs p;
+  for (int g = 0; g < kMaxPeers; g++) p.mailbox[g] = g < world ? static_cast<MailSlot*>(mailboxes[g]) : nullptr;
+  p.seq = seq; p.world = world; p.rank = rank;
+  if (!p.mailbox[rank]) { set_error("dot collect: own mailbox is null"); return B200_EINVAL; }
+  if (elem_bytes == 8)
+    dot_collect_kernel<double><<<1, 32, 0, stream>>>(p, static_cast<double*>(result_dev), static_cast<double*>(result_host), nullptr, 0);
+  else
+    dot_collect_kernel<float><<<1, 32, 0, stream>>>(p, static_cast<float*>(result_dev), static_cast<float*>(result_host), nullptr, 0);
+  count_launch();
+  B200_CUDA(cudaPeekAtLastError());
+  return B200_OK;
 }
 
 }  // namespace b200

@@ -96,6 +96,7 @@ struct DotCall {
   int p2p_world = 0, p2p_rank = 0;
   unsigned long long p2p_seq = 0;
   void* const* p2p_mailboxes = nullptr;
+  bool p2p_send_only = false;  // the sending half only; launch_dot_collect sums later
   Bell bell;  // only .flag and .seq are used: dot has its own ticket
   Resolved r;
   Geometry g;
@@ -103,13 +104,15 @@ struct DotCall {
   cudaStream_t stream;
 };
 int launch_dot_impl(const DotCall& call);
+int launch_dot_collect(int elem_bytes, void* result_dev, void* result_host, int world, int rank, unsigned long long seq,
+                       void* const* mailboxes, cudaStream_t stream);
 
 // shared bodies of the LEVEL 1 launchers (api.cu), also called by LEVEL 2 with a doorbell
 int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1, double s2,
               const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream);
 int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
                       void* result_host_mapped, int world, int rank, unsigned long long seq, void* const* mailboxes,
-                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream);
+                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream, bool send_only = false);
 
 int launch_copy_bulk(const void* src, void* dst, size_t bytes, const Resolved& r, const DeviceProps& props,
                      cudaStream_t stream);

@@ -442,25 +442,30 @@ template <typename T> __device__ __forceinline__ T from_bits(unsigned long long 
 template <> __device__ __forceinline__ double from_bits<double>(unsigned long long b) { return __longlong_as_double((long long)b); }
 template <> __device__ __forceinline__ float from_bits<float>(unsigned long long b) { return __uint_as_float((unsigned)b); }
 
-// Called by warp 0 of the last block; `mine` is this GPU's partial.  Returns the all-reduced sum
-// (identical on every GPU) in every lane.
-// Only the MODE == 2 instantiations of dot_kernel contain this code: inlined or not, it raises the
-// kernel's register allocation from 38 to 42, which drops the residency of 512-thread blocks from 3
-// to 2 per SM (-3.5 % at 2^29) -- so single-GPU, NCCL and host-combine runs use the lean kernel, and
-// the MODE 2 kernel is register-capped by its launch bound instead (the spills land in this
-// once-per-launch code).  `pp` points INTO the __grid_constant__ parameter block: nothing is copied.
+// The all-reduce has two halves, usable separately (DOT_TICKET_SEND + dot_collect_kernel) by callers that
+// do not need the sum at once: send early, collect late, and the wait for the slowest GPU hides under
+// whatever runs in between.
+// send: lanes < world of one warp store {bits, seq} into slot `rank` of every GPU's mailbox.
 template <typename T>
-__device__ __noinline__ T p2p_allreduce_warp(const P2PArgs* pp, T mine) {
-  const P2PArgs& p = *pp;
+__device__ __forceinline__ void p2p_send_warp(const P2PArgs& p, T mine) {
   const int lane = threadIdx.x & 31;
-  bool ok = true;
-  T got = T(0);
   const int bank = (int)(p.seq & 1ull) * kMaxPeers;
   if (lane < p.world) {
     MailSlot* dst = p.mailbox[lane] + bank + p.rank;   // my slot in GPU `lane`'s mailbox
     st_relaxed_sys(&dst->bits, to_bits<T>(mine));
-    st_release_sys(&dst->seq, p.seq);           // value is visible before the sequence number
-    const MailSlot* src = p.mailbox[p.rank] + bank + lane;  // GPU `lane`'s slot in my mailbox (local HBM)
+    st_release_sys(&dst->seq, p.seq);                  // value is visible before the sequence number
+  }
+}
+// collect: one full warp waits for the `world` slots of its OWN mailbox (local HBM) to carry p.seq and
+// adds them in rank order; the sum (identical on every GPU) is returned in every lane.
+template <typename T>
+__device__ __forceinline__ T p2p_collect_warp(const P2PArgs& p) {
+  const int lane = threadIdx.x & 31;
+  const int bank = (int)(p.seq & 1ull) * kMaxPeers;
+  bool ok = true;
+  T got = T(0);
+  if (lane < p.world) {
+    const MailSlot* src = p.mailbox[p.rank] + bank + lane;  // GPU `lane`'s slot in my mailbox
     const unsigned long long t0 = global_timer_ns();
     while (ld_acquire_sys(&src->seq) != p.seq) {
       if (global_timer_ns() - t0 > 2000000000ull) { ok = false; break; }
@@ -471,6 +476,20 @@ __device__ __noinline__ T p2p_allreduce_warp(const P2PArgs* pp, T mine) {
   for (int r = 0; r < p.world; r++) total = add_rn(total, __shfl_sync(0xffffffffu, got, r));  // rank order
   if (!__all_sync(0xffffffffu, ok)) total = from_bits<T>(~0ull);  // NaN: a peer never arrived
   return total;
+}
+
+// Called by warp 0 of the last block; `mine` is this GPU's partial.  Returns the all-reduced sum
+// (identical on every GPU) in every lane.
+// Only the MODE >= 2 instantiations of dot_kernel contain this code: inlined or not, it raises the
+// kernel's register allocation from 38 to 42, which drops the residency of 512-thread blocks from 3
+// to 2 per SM (-3.5 % at 2^29) -- so single-GPU, NCCL and host-combine runs use the lean kernel, and
+// the MODE 2/3 kernels are register-capped by their launch bound instead (the spills land in this
+// once-per-launch code).  `pp` points INTO the __grid_constant__ parameter block: nothing is copied.
+template <typename T, bool COLLECT>
+__device__ __noinline__ T p2p_allreduce_warp(const P2PArgs* pp, T mine) {
+  p2p_send_warp<T>(*pp, mine);
+  if constexpr (COLLECT) return p2p_collect_warp<T>(*pp);
+  else return mine;
 }
 
 struct DotArgs {
@@ -494,12 +513,13 @@ constexpr int dot_max_block(int vb, int unroll) { return vb * unroll >= 128 ? 51
 // MODE: how the block partials become the result
 enum DotMode : int { DOT_TWO_PASS = 0,    // partials only; dot_final_kernel follows
                      DOT_TICKET = 1,      // the last block to finish runs the second pass
-                     DOT_TICKET_P2P = 2 };// ... and then the all-reduce over peer memory
-// the P2P instantiation runs with at most 512 threads and must keep 3 blocks of them resident
+                     DOT_TICKET_P2P = 2,  // ... and then the all-reduce over peer memory
+                     DOT_TICKET_SEND = 3 };// ... and then only SENDS its partial to the peers (dot_collect_kernel sums later)
+// the P2P instantiations run with at most 512 threads and must keep 3 blocks of them resident
 constexpr int dot_block_bound(int vb, int unroll, int mode) {
-  return mode == DOT_TICKET_P2P ? 512 : dot_max_block(vb, unroll);
+  return mode >= DOT_TICKET_P2P ? 512 : dot_max_block(vb, unroll);
 }
-constexpr int dot_min_blocks(int vb, int unroll, int mode) { return (mode == DOT_TICKET_P2P && vb * unroll <= 32) ? 3 : 1; }
+constexpr int dot_min_blocks(int vb, int unroll, int mode) { return (mode >= DOT_TICKET_P2P && vb * unroll <= 32) ? 3 : 1; }
 
 template <typename T, int VB, int UNROLL, int HINT, bool FUSED, int MODE>
 __global__ void __launch_bounds__(dot_block_bound(VB, UNROLL, MODE), dot_min_blocks(VB, UNROLL, MODE))
@@ -581,10 +601,10 @@ dot_kernel(const __grid_constant__ DotArgs args) {
     if (is_last) {
       T v = dot_second_pass<T>(partials, gridDim.x, scratch);
       if (threadIdx.x == 0) *args.ticket = 0u;  // ready for the next launch
-      if constexpr (MODE == DOT_TICKET_P2P) {   // fused all-reduce over peer memory
+      if constexpr (MODE >= DOT_TICKET_P2P) {   // fused all-reduce over peer memory (or its sending half)
         if (threadIdx.x == 0) scratch[0] = v;
         __syncthreads();
-        if (threadIdx.x < 32) v = p2p_allreduce_warp<T>(&args.p2p, scratch[0]);
+        if (threadIdx.x < 32) v = p2p_allreduce_warp<T, MODE == DOT_TICKET_P2P>(&args.p2p, scratch[0]);
       }
       if (threadIdx.x == 0) {
         if (args.result_dev) *static_cast<T*>(args.result_dev) = v;
@@ -592,6 +612,19 @@ dot_kernel(const __grid_constant__ DotArgs args) {
         if (args.bell_flag) ring_host(args.bell_flag, args.bell_seq);  // release: after the result
       }
     }
+  }
+}
+
+// The collecting half of the split all-reduce: one warp.
+template <typename T>
+__global__ void __launch_bounds__(32)
+dot_collect_kernel(const __grid_constant__ P2PArgs p, T* result_dev, T* result_host, unsigned long long* bell_flag,
+                   unsigned long long bell_seq) {
+  const T v = p2p_collect_warp<T>(p);
+  if (threadIdx.x == 0) {
+    if (result_dev) *result_dev = v;
+    if (result_host) *result_host = v;
+    if (bell_flag) ring_host(bell_flag, bell_seq);
   }
 }
 

@@ -106,6 +106,8 @@ def lib() -> C.CDLL:
         "b200_launch_dot": (ci, [vp, vp, sz, ci, vp, vp, vp, cfgp, vp]),
         "b200_dot_mailbox_bytes": (sz, []),
         "b200_launch_dot_allreduce_p2p": (ci, [vp, vp, sz, ci, vp, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
+        "b200_launch_dot_send_p2p": (ci, [vp, vp, sz, ci, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
+        "b200_launch_dot_collect_p2p": (ci, [ci, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), vp]),
         "b200_launch_doorbell": (ci, [ci, vp, vp, vp, sz, ci, d, d, d, cfgp, C.POINTER(Doorbell), vp]),
         "b200_launch_dot_doorbell": (ci, [vp, vp, sz, ci, vp, vp, vp, cfgp, C.POINTER(Doorbell), vp]),
         "b200_dot_mailbox_create": (ci, [C.POINTER(vp)]),
@@ -223,6 +225,22 @@ def launch_dot_allreduce_p2p(a: int, b: int, n: int, elem_bytes: int, workspace:
     _check(lib().b200_launch_dot_allreduce_p2p(a, b, n, elem_bytes, workspace, result_dev or None, result_host_mapped or None,
                                                world, rank, seq, boxes, C.byref(cfg) if cfg is not None else None,
                                                C.c_void_p(stream)))
+
+
+def launch_dot_send_p2p(a: int, b: int, n: int, elem_bytes: int, workspace: int, *, world: int, rank: int, seq: int,
+                        mailboxes, partial_dev: int = 0, cfg: LaunchCfg | None = None, stream: int = 0) -> None:
+    """LEVEL 1: the sending half of the fused all-reduce (no wait); pair with launch_dot_collect_p2p."""
+    boxes = (C.c_void_p * len(mailboxes))(*mailboxes)
+    _check(lib().b200_launch_dot_send_p2p(a, b, n, elem_bytes, workspace, partial_dev or None, world, rank, seq, boxes,
+                                          C.byref(cfg) if cfg is not None else None, C.c_void_p(stream)))
+
+
+def launch_dot_collect_p2p(elem_bytes: int, result_dev: int, *, world: int, rank: int, seq: int, mailboxes,
+                           result_host_mapped: int = 0, stream: int = 0) -> None:
+    """LEVEL 1: one-warp kernel that waits for the partials of call `seq` and adds them in rank order."""
+    boxes = (C.c_void_p * len(mailboxes))(*mailboxes)
+    _check(lib().b200_launch_dot_collect_p2p(elem_bytes, result_dev or None, result_host_mapped or None, world, rank, seq,
+                                             boxes, C.c_void_p(stream)))
 
 
 def launch_doorbell(kernel: str, a: int, b: int, c: int, n: int, elem_bytes: int, bell: Doorbell, *,

@@ -229,11 +229,24 @@ def main():
     combine = "none" if dist is None else ("p2p" if boxes is not None else "nccl")
     dot_seq = [0]
 
+    def collect():
+        # the second half of the split all-reduce: a one-warp kernel that adds the partials of the last send
+        if combine == "p2p" and dot_seq[0] > 0 and pending[0] == "sent":
+            bs.launch_dot_collect_p2p(eb, dot_out.data_ptr(), world=world, rank=rank, seq=dot_seq[0], mailboxes=boxes.ptrs,
+                                      stream=st)
+            pending[0] = None
+
     def enqueue(kernel):
         if kernel == "dot" and combine == "p2p":
+            # Nothing later in the step depends on the sum, so the all-reduce is split: the dot kernel SENDS
+            # its partial to every peer's mailbox over NVLink and returns; the partials are collected just
+            # before the next dot (and at the end of the timed region), so the wait for the slowest rank
+            # hides under nstream/copy/mul/add/triad.  (The blocking e2e path below uses the fused call.)
+            collect()
             dot_seq[0] += 1   # same count on every rank
-            bs.launch_dot_allreduce_p2p(pa, pb, n, eb, ws.data_ptr(), dot_out.data_ptr(), world=world, rank=rank,
-                                        seq=dot_seq[0], mailboxes=boxes.ptrs, stream=st)
+            bs.launch_dot_send_p2p(pa, pb, n, eb, ws.data_ptr(), world=world, rank=rank, seq=dot_seq[0],
+                                   mailboxes=boxes.ptrs, stream=st)
+            pending[0] = "sent"
         elif kernel == "dot":
             if pending[0] is not None:
                 pending[0].wait()      # the previous step's all-reduce still owns dot_out
@@ -257,6 +270,7 @@ def main():
     for _ in range(W):
         for k in KERNEL_ORDER:
             enqueue(k)
+    collect()
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -274,7 +288,10 @@ def main():
             enqueue(k)
             ev[i].record()
             i += 1
-    if pending[0] is not None:
+    if pending[0] == "sent":
+        collect()
+        ev[-1].record()            # the timed region ends when the last sum has been collected
+    elif pending[0] is not None:
         pending[0].wait()
         ev[-1].record()            # the timed region ends when the last all-reduce has landed
     torch.cuda.synchronize()
@@ -368,7 +385,7 @@ def main():
                    "bytes_per_step_per_gpu": step_bytes,
                    "l2": f"inputs larger than L2: 3 arrays x {n * eb / 1e6:.0f} MB per GPU vs 126 MB L2, no flush needed",
                    "parallelism": (f"{world} ranks (one process per GPU), contiguous shards, no collective for the elementwise kernels; "
-                                   + ("dot: partials all-reduced inside the dot kernel over NVLink peer memory (CUDA IPC mailboxes), one launch, no NCCL"
+                                   + ("dot: partials exchanged by the dot kernel itself over NVLink peer memory (CUDA IPC mailboxes), no NCCL; device-timed path: send in the dot kernel, one-warp collect before the next dot; blocking e2e path: fused send+collect in one launch"
                                       if combine == "p2p" else
                                       "dot: one NCCL all-reduce of 1 element per step, overlapped with the following kernels"))
                                   if world > 1 else "1 GPU",

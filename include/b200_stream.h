@@ -138,6 +138,19 @@ int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int el
                                   unsigned long long seq, void* const* mailboxes, const b200_launch_cfg* cfg,
                                   void* stream);
 
+/* The same all-reduce in two halves, for ASYNCHRONOUS callers that do not need the sum at once: `send`
+ * is the dot kernel whose last block stores the partial into every peer's mailbox and returns without
+ * waiting (partial_dev, may be NULL, receives this GPU's partial); `collect` is a one-warp kernel that
+ * waits for the `world` partials of call `seq` in the GPU's own mailbox, adds them in rank order (same
+ * bits as the fused call) and stores the sum.  Whatever is enqueued between the two hides the wait for
+ * the slowest GPU.  Rule: on every GPU, collect(seq) must be enqueued before the next send (the
+ * mailbox has two banks). */
+int b200_launch_dot_send_p2p(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* partial_dev,
+                             int world, int rank, unsigned long long seq, void* const* mailboxes,
+                             const b200_launch_cfg* cfg, void* stream);
+int b200_launch_dot_collect_p2p(int elem_bytes, void* result_dev, void* result_host_mapped, int world, int rank,
+                                unsigned long long seq, void* const* mailboxes, void* stream);
+
 /* Completion doorbell: lets a BLOCKING caller learn that a kernel has finished without
  * cudaStreamSynchronize.  Every block takes a ticket once its stores are fenced; the block that takes
  * the last one stores `seq` (release, system scope) to a word of mapped pinned host memory, which the

@@ -53,6 +53,31 @@ def main():
                 dist.all_gather_object(allv, v1.tobytes())
                 assert all(x == allv[0] for x in allv), "ranks disagree on the all-reduced dot"
             s.join_group(1, 0, [])
+            # LEVEL 1, the split all-reduce: send in the dot kernel, collect later -- same bits as the fused call
+            mb2 = connect_mailboxes(dist, rank, world)
+            assert mb2 is not None
+            s.write_arrays(a0[begin:begin + max(count, 1)], b0[begin:begin + max(count, 1)], None)
+            info = s.shard_info(0)
+            tt = torch.float64 if dtype is np.float64 else torch.float32
+            ws = torch.zeros(bs.dot_workspace_bytes(), dtype=torch.uint8, device="cuda")
+            out = torch.zeros(1, dtype=tt, device="cuda")
+            part = torch.zeros(1, dtype=tt, device="cuda")
+            st = torch.cuda.current_stream().cuda_stream
+            eb = np.dtype(dtype).itemsize
+            torch.cuda.synchronize()
+            for seq in range(1, 6):
+                bs.launch_dot_send_p2p(info["a"], info["b"], info["count"], eb, ws.data_ptr(), world=world, rank=rank,
+                                       seq=seq, mailboxes=mb2.ptrs, partial_dev=part.data_ptr(), stream=st)
+                if rank == world - 1 and seq == 3:
+                    torch.cuda.synchronize()
+                    import time
+                    time.sleep(0.2)          # a late collector must still find its bank intact
+                bs.launch_dot_collect_p2p(eb, out.data_ptr(), world=world, rank=rank, seq=seq, mailboxes=mb2.ptrs, stream=st)
+                torch.cuda.synchronize()
+                assert out.cpu().numpy()[0].tobytes() == want.tobytes(), (rank, seq)
+                assert part.cpu().numpy()[0].tobytes() == partial.tobytes(), (rank, seq)
+            dist.barrier()
+            mb2.close()
         dist.barrier()
     mb.close()
     dist.barrier()
