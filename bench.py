@@ -229,23 +229,36 @@ def main():
     combine = "none" if dist is None else ("p2p" if boxes is not None else "nccl")
     dot_seq = [0]
 
+    side = torch.cuda.Stream() if combine == "p2p" else None   # where the collecting half runs
+    ev_sent = torch.cuda.Event() if combine == "p2p" else None
+    ev_collected = torch.cuda.Event() if combine == "p2p" else None
+
+    def collect_async():
+        # the second half of the split all-reduce: a one-warp kernel on a SIDE stream (as NCCL's kernel
+        # would be), after the send; the main stream only waits for it before the next send
+        ev_sent.record()
+        side.wait_event(ev_sent)
+        bs.launch_dot_collect_p2p(eb, dot_out.data_ptr(), world=world, rank=rank, seq=dot_seq[0], mailboxes=boxes.ptrs,
+                                  stream=side.cuda_stream)
+        ev_collected.record(side)
+
     def collect():
-        # the second half of the split all-reduce: a one-warp kernel that adds the partials of the last send
-        if combine == "p2p" and dot_seq[0] > 0 and pending[0] == "sent":
-            bs.launch_dot_collect_p2p(eb, dot_out.data_ptr(), world=world, rank=rank, seq=dot_seq[0], mailboxes=boxes.ptrs,
-                                      stream=st)
+        if combine == "p2p" and pending[0] == "sent":
+            torch.cuda.current_stream().wait_event(ev_collected)
             pending[0] = None
 
     def enqueue(kernel):
         if kernel == "dot" and combine == "p2p":
             # Nothing later in the step depends on the sum, so the all-reduce is split: the dot kernel SENDS
-            # its partial to every peer's mailbox over NVLink and returns; the partials are collected just
-            # before the next dot (and at the end of the timed region), so the wait for the slowest rank
-            # hides under nstream/copy/mul/add/triad.  (The blocking e2e path below uses the fused call.)
+            # its partial to every peer's mailbox over NVLink and returns; a one-warp kernel on a side stream
+            # collects the partials, and the main stream joins it only before the next dot (and at the end
+            # of the timed region), so the wait for the slowest rank hides under nstream/copy/mul/add/triad.
+            # (The blocking e2e path below uses the fused call.)
             collect()
             dot_seq[0] += 1   # same count on every rank
             bs.launch_dot_send_p2p(pa, pb, n, eb, ws.data_ptr(), world=world, rank=rank, seq=dot_seq[0],
                                    mailboxes=boxes.ptrs, stream=st)
+            collect_async()
             pending[0] = "sent"
         elif kernel == "dot":
             if pending[0] is not None:
@@ -385,7 +398,7 @@ def main():
                    "bytes_per_step_per_gpu": step_bytes,
                    "l2": f"inputs larger than L2: 3 arrays x {n * eb / 1e6:.0f} MB per GPU vs 126 MB L2, no flush needed",
                    "parallelism": (f"{world} ranks (one process per GPU), contiguous shards, no collective for the elementwise kernels; "
-                                   + ("dot: partials exchanged by the dot kernel itself over NVLink peer memory (CUDA IPC mailboxes), no NCCL; device-timed path: send in the dot kernel, one-warp collect before the next dot; blocking e2e path: fused send+collect in one launch"
+                                   + ("dot: partials exchanged by the dot kernel itself over NVLink peer memory (CUDA IPC mailboxes), no NCCL; device-timed path: send in the dot kernel, one-warp collect on a side stream, joined before the next dot; blocking e2e path: fused send+collect in one launch"
                                       if combine == "p2p" else
                                       "dot: one NCCL all-reduce of 1 element per step, overlapped with the following kernels"))
                                   if world > 1 else "1 GPU",
