@@ -224,3 +224,72 @@ def test_two_rank_sharded_path_matches_unsharded_oracle(orc):
     assert pos == n
     assert abs(total - want) <= 1e7 * np.finfo(np.float64).eps * abs(want)   # src/main.cpp:384
     assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, np.float64(total)) == 0
+
+
+def _mailbox_rank_main(rank, world, port, q):
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from babelstream_b200.group import connect_mailboxes
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    mb = connect_mailboxes(dist, rank, world)
+    q.put((rank, mb is None, connect_mailboxes.last_error))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(bs.device_count() > 0, reason="only meaningful on a machine without a GPU")
+def test_mailbox_exchange_fails_collectively_without_gpus():
+    """bench.py's N > 1 bring-up: when no rank can create a mailbox (no device here), EVERY rank gets None
+    (so all of them take the NCCL fallback together) and the reason names each rank."""
+    import torch.multiprocessing as mp
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_mailbox_rank_main, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert [g[1] for g in got] == [True, True]
+    assert all("rank 0" in g[2] and "rank 1" in g[2] for g in got)
+
+
+def test_mailbox_bank_protocol_model():
+    """A sequential model of the two-bank mailbox protocol of csrc/kernels.cuh, explored over random
+    interleavings: per GPU the program is  send(1) collect(1) send(2) collect(2) ...  (collect k before
+    send k+1, the documented rule); a collect may only run when all its slots carry its sequence number.
+    Whatever the schedule, no slot is overwritten before every peer has read it, and no rank deadlocks."""
+    import random
+    for world in (2, 3, 8):
+        for trial in range(200):
+            rng = random.Random(world * 1000 + trial)
+            steps = 6
+            slots = [[[0] * world for _ in range(2)] for _ in range(world)]   # [owner][bank][sender] = seq
+            read = [[[0] * world for _ in range(2)] for _ in range(world)]    # last seq the owner consumed
+            pc = [0] * world                                                   # 2*(k-1) = send k, 2*(k-1)+1 = collect k
+            while any(p < 2 * steps for p in pc):
+                ready = []
+                for g in range(world):
+                    if pc[g] >= 2 * steps:
+                        continue
+                    k = pc[g] // 2 + 1
+                    if pc[g] % 2 == 0 or all(slots[g][k & 1][s] == k for s in range(world)):
+                        ready.append(g)
+                assert ready, ("deadlock", world, trial, pc)
+                g = rng.choice(ready)
+                k = pc[g] // 2 + 1
+                if pc[g] % 2 == 0:       # send k: overwrite my slot in everyone's bank k&1
+                    for owner in range(world):
+                        old = slots[owner][k & 1][g]
+                        assert old == 0 or read[owner][k & 1][g] == old, ("overwrote an unread partial", world, trial)
+                        slots[owner][k & 1][g] = k
+                else:                    # collect k
+                    for s in range(world):
+                        assert slots[g][k & 1][s] == k
+                        read[g][k & 1][s] = k
+                pc[g] += 1
