@@ -387,17 +387,22 @@ __device__ __forceinline__ T dot_second_pass(const T* partials, unsigned nparts,
 // ------------------------------------------------------------------------------------------------
 // Fused dot + all-reduce over NVLink peer memory (no NCCL, no extra launch).
 // Every GPU owns a mailbox of kMaxPeers slots in its own HBM, mapped into all peers.  The last block
-// of GPU r's dot kernel  (1) stores {value, seq} into slot r of EVERY GPU's mailbox with
-// system-scope release semantics (peer stores travel over NVLink / NVSwitch),  (2) waits until all G
-// slots of its OWN mailbox carry this call's sequence number,  (3) adds the G values in rank order.
-// Every GPU ends up with the same bits.  The G kernels run on G different devices at the same
-// time, so the wait cannot deadlock on scheduling; a globaltimer bound turns a missing peer into a
-// NaN result instead of a hang.
+// of GPU r's dot kernel  (1) stores its partial into slot r of EVERY GPU's mailbox (peer stores travel
+// over NVLink / NVSwitch),  (2) waits until all G slots of its OWN mailbox carry this call's sequence
+// number,  (3) adds the G values in rank order.  Every GPU ends up with the same bits.  The G kernels
+// run on G different devices at the same time, so the wait cannot deadlock on scheduling; a
+// globaltimer bound turns a missing peer into a NaN result instead of a hang.
+//
+// Wire format: every 8-byte word of a slot carries its own flag -- {payload: 32 bits, flag = low 32
+// bits of seq} -- and an aligned 8-byte store is single-copy atomic, so a word is valid exactly when
+// its flag matches.  The sender needs NO release fence (which would hold the kernel until every peer
+// store has been acknowledged across NVLink) and the receiver no acquire: a double travels as two such
+// words, a float as one, all stored and polled with relaxed system-scope accesses.  (The layout NCCL's
+// low-latency protocol uses for the same reason.)
 // ------------------------------------------------------------------------------------------------
 constexpr int kMaxPeers = 8;
 struct alignas(16) MailSlot {
-  unsigned long long seq;
-  unsigned long long bits;
+  unsigned long long w[2];  // w[i] = (flag << 32) | payload_i ; payload_0 = low half of the value's bits
 };
 // A mailbox is TWO banks of kMaxPeers slots, used alternately (bank = seq & 1).  GPU A can only start
 // call k+2 after it has finished call k+1, which needed B's partial of k+1, which B sent after it had
@@ -408,14 +413,6 @@ constexpr size_t kMailboxBytes = sizeof(MailSlot) * kMaxPeers * kMailBanks;
 
 __device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
 }
 __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
   unsigned long long v;
@@ -452,8 +449,9 @@ __device__ __forceinline__ void p2p_send_warp(const P2PArgs& p, T mine) {
   const int bank = (int)(p.seq & 1ull) * kMaxPeers;
   if (lane < p.world) {
     MailSlot* dst = p.mailbox[lane] + bank + p.rank;   // my slot in GPU `lane`'s mailbox
-    st_relaxed_sys(&dst->bits, to_bits<T>(mine));
-    st_release_sys(&dst->seq, p.seq);                  // value is visible before the sequence number
+    const unsigned long long bits = to_bits<T>(mine), flag = (p.seq & 0xffffffffull) << 32;
+    st_relaxed_sys(&dst->w[0], flag | (bits & 0xffffffffull));
+    if constexpr (sizeof(T) == 8) st_relaxed_sys(&dst->w[1], flag | (bits >> 32));
   }
 }
 // collect: one full warp waits for the `world` slots of its OWN mailbox (local HBM) to carry p.seq and
@@ -466,11 +464,16 @@ __device__ __forceinline__ T p2p_collect_warp(const P2PArgs& p) {
   T got = T(0);
   if (lane < p.world) {
     const MailSlot* src = p.mailbox[p.rank] + bank + lane;  // GPU `lane`'s slot in my mailbox
+    const unsigned long long flag = p.seq & 0xffffffffull;
     const unsigned long long t0 = global_timer_ns();
-    while (ld_acquire_sys(&src->seq) != p.seq) {
+    unsigned long long w0, w1 = flag << 32;
+    for (;;) {
+      w0 = ld_relaxed_sys(&src->w[0]);
+      if constexpr (sizeof(T) == 8) w1 = ld_relaxed_sys(&src->w[1]);
+      if ((w0 >> 32) == flag && (w1 >> 32) == flag) break;
       if (global_timer_ns() - t0 > 2000000000ull) { ok = false; break; }
     }
-    got = from_bits<T>(ld_relaxed_sys(&src->bits));
+    got = from_bits<T>((w0 & 0xffffffffull) | (w1 << 32));
   }
   T total = T(0);
   for (int r = 0; r < p.world; r++) total = add_rn(total, __shfl_sync(0xffffffffu, got, r));  // rank order
