@@ -382,8 +382,15 @@ class B200Stream:
         return tuple(out)
 
     # -- extras --------------------------------------------------------------------------------
-    def read_arrays(self):
-        a, b, c = (np.empty(self.array_size, dtype=self.dtype) for _ in range(3))
+    def read_arrays(self, out=None):
+        """Gather the shards into host arrays: fresh ones, or the caller's `out = (a, b, c)` (e.g. views of
+        pinned memory; C-contiguous, dtype and length of the model)."""
+        if out is None:
+            out = tuple(np.empty(self.array_size, dtype=self.dtype) for _ in range(3))
+        for x in out:
+            if x.dtype != self.dtype or x.size != self.array_size or not x.flags.c_contiguous or not x.flags.writeable:
+                raise ValueError("read_arrays: out arrays must be writable, C-contiguous, of the model's dtype and length")
+        a, b, c = out
         _check(lib().b200_read_arrays(self._h, a.ctypes.data, b.ctypes.data, c.ctypes.data))
         return a, b, c
 

@@ -347,6 +347,41 @@ def main():
     e2e_s = time.perf_counter() - t0
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+
+    # ---- supplementary: the same step fed from and drained to HOST buffers -------------------------
+    # Not the reference's metric (Stream<T> has no per-step host inputs, see `e2e.how`), reported so that
+    # the cost of moving the arrays over PCIe every step can be read next to it: pinned host a, b, c ->
+    # b200_write_arrays (H2D) -> the six blocking kernels -> b200_read_arrays (D2H), host clock.
+    host_buffers = None
+    if world == 1:
+        try:
+            hk = 3
+            pinned = [torch.empty(n, dtype=torch.float64).pin_memory() for _ in range(3)]
+            hv = [p.numpy() for p in pinned]
+            for x, v in zip(hv, (0.1, 0.2, 0.0)):
+                x.fill(v)
+
+            def host_step():
+                s.write_arrays(*hv)
+                for k in KERNEL_ORDER:
+                    s.run(k)
+                s.read_arrays(out=hv)
+
+            host_step()
+            t0 = time.perf_counter()
+            for _ in range(hk):
+                host_step()
+            hs = (time.perf_counter() - t0) / hk
+            host_buffers = {"value": round(step_bytes / hs / 1e9, 1), "unit": UNIT, "ms_per_step": round(hs * 1e3, 3),
+                            "steps": hk, "h2d_bytes_per_step": 3 * n * eb, "d2h_bytes_per_step": 3 * n * eb + eb,
+                            "pcie_gbs": round(2 * 3 * n * eb / hs / 1e9, 1),
+                            "how": "supplementary, PCIe-bound: every step copies a, b, c from pinned host memory "
+                                   "(b200_write_arrays), runs the six blocking kernels and copies a, b, c back "
+                                   "(b200_read_arrays); the reference never does this per step -- its arrays are "
+                                   "device-resident and get_arrays runs once after the timed loop (src/main.cpp:291-294)"}
+            del pinned, hv
+        except Exception as e:  # noqa: BLE001
+            host_buffers = {"error": str(e)[:200]}
     ga, gb, gc = s.get_arrays()
     # cheap sanity on the e2e arrays: every element equal (the inputs are constants), finite
     sane = bool(np.isfinite(ga[0]) and (ga == ga[0]).all() and (gb == gb[0]).all() and (gc == gc[0]).all())
@@ -420,6 +455,8 @@ def main():
                        "kernel arguments only on the way in, dot's sum read back every step", "sane": sane},
         "gpu_launches": int(launches), "clocks": clocks, "dot_last": dot_value,
     }
+    if host_buffers is not None:
+        line["e2e_host_buffers"] = host_buffers
 
     # ---- CPU baseline and extras (rank 0, N = 1 only) ---------------------------------------------
     if world == 1:

@@ -239,13 +239,13 @@ def test_driver_cli_matrix(args):
 
 
 @needs_bin
-@needs_bin
 def test_driver_managed_memory():
     p = run_bin("-s", str((1 << 22) + 3), "-n", "10", "--only", "All", env={"BABELSTREAM_B200_MEM": "managed"})
     assert p.returncode == 0, p.stdout + p.stderr
     assert "MANAGED" in p.stdout
 
 
+@needs_bin
 def test_driver_csv_and_contract_off():
     p = run_bin("-s", "4194304", "-n", "20", "--csv", "--only", "All", env={"BABELSTREAM_B200_CONTRACT": "off"})
     assert p.returncode == 0, p.stdout + p.stderr
@@ -254,6 +254,20 @@ def test_driver_csv_and_contract_off():
     assert all(int(r[2]) == 4194304 and int(r[3]) == 8 and float(r[4]) > 0 for r in rows)
     header = [l for l in p.stdout.splitlines() if l.startswith("function,")]
     assert header and header[0].split(",")[4] == "max_MB_per_sec"
+
+
+@needs_bin
+@pytest.mark.parametrize("args", [
+    ["-s", str(1 << 29), "-n", "3", "--only", "All"],    # the north-star size: 3 x 4.29 GB
+    ["-s", str(1 << 30), "-n", "3", "--only", "Triad"],  # BASELINE config 4 on one GPU: 3 x 8.59 GB
+])
+def test_driver_full_sizes_pass_check_solution(args):
+    """BASELINE.json's full sizes through the size-independent property the domain offers: the reference's
+    own check_solution (src/main.cpp:331-421) walks EVERY element of a, b, c against the gold recurrence
+    and checks dot against goldA*goldB*n; the exit code is its verdict."""
+    p = run_bin(*args)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "FAILED validation" not in p.stderr and "Triad" in p.stdout
 
 
 @needs_bin
