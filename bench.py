@@ -468,11 +468,17 @@ def main():
             extras = {}
             b200_bin = os.path.join(ROOT, "build", "b200-stream")
             cuda_bin = os.path.join(ROOT, "oracle", "_ref", "cuda-stream")
+            thrust_bin = os.path.join(ROOT, "oracle", "_ref", "thrust-stream")  # second library baseline
             try:
                 if os.path.exists(b200_bin):
                     extras["b200_stream_driver"] = {k: round(v["gbs"], 1) for k, v in run_stream_binary(b200_bin, n, 100).items()}
                 if os.path.exists(cuda_bin):
                     extras["reference_cuda_stream_driver"] = {k: round(v["gbs"], 1) for k, v in run_stream_binary(cuda_bin, n, 100).items()}
+                if os.path.exists(thrust_bin):
+                    try:
+                        extras["reference_thrust_stream_driver"] = {k: round(v["gbs"], 1) for k, v in run_stream_binary(thrust_bin, n, 100).items()}
+                    except Exception as e:  # noqa: BLE001  (a library baseline must not cost the other extras)
+                        extras["reference_thrust_stream_driver"] = {"error": str(e)[:200]}
                 big = 1 << 29
                 if os.path.exists(b200_bin):
                     r = run_stream_binary(b200_bin, big, 30, only="Triad")
@@ -483,6 +489,9 @@ def main():
                     if os.path.exists(cuda_bin):
                         r2 = run_stream_binary(cuda_bin, big, 30, only="Triad")
                         extras["north_star_triad_2^29"]["reference_cuda_stream_driver_gbs"] = round(r2["triad"]["gbs"], 1)
+                    if os.path.exists(thrust_bin) and "error" not in extras.get("reference_thrust_stream_driver", {}):
+                        r3 = run_stream_binary(thrust_bin, big, 30, only="Triad")
+                        extras["north_star_triad_2^29"]["reference_thrust_stream_driver_gbs"] = round(r3["triad"]["gbs"], 1)
             except Exception as e:  # noqa: BLE001
                 extras["error"] = str(e)[:300]
             line["driver"] = extras
