@@ -7,7 +7,9 @@
 //            spinning on per-worker counters, so that the G launches start together instead of
 //            one after another from a single thread (SURVEY.md section 7 "launch skew").
 // The elementwise kernels never communicate.  dot is the one exchange step: each GPU reduces its
-// shard to one T, and the G values are combined by ONE ncclAllReduce over NVLink (count = 1).
+// shard to one T, and the G values are combined inside the dot kernel by peer stores over NVLink
+// (dot_combine=p2p, the default when every GPU pair has peer access), by ONE ncclAllReduce of
+// count 1 (nccl) or by a rank-order sum of G mapped host scalars (host).
 #include <dlfcn.h>
 #include <nccl.h>  // types only: the library is dlopen'ed, so single-GPU use needs no NCCL at all
 

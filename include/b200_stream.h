@@ -207,7 +207,8 @@ void b200_destroy(b200_ctx* ctx);
  * other processes, each holding its own contiguous shard.  From then on b200_dot returns the sum over
  * ALL ranks, computed by the fused peer-memory all-reduce inside the dot kernel (no NCCL, no extra
  * launch); every rank must call b200_dot the same number of times.  mailboxes[g] is rank g's mailbox as
- * mapped into this process (see b200_ipc_open); the array is copied.  world = 1 leaves the group. */
+ * mapped into this process (see b200_ipc_open); the array is copied.  world = 1 leaves the group.
+ * The call counter restarts at every join, so the mailboxes of a NEW group must be fresh (zeroed) ones. */
 int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes);
 
 /* "key=value" tuning / behaviour options, also read from the environment at create time as
