@@ -136,6 +136,11 @@ struct b200_ctx {
   bool managed = false;
   void* managed_base[3] = {nullptr, nullptr, nullptr};
   bool managed_on_host = false;  // get_arrays moved the pages to the CPU; move them back before the next kernel
+  // mem=pagefault: the reference's MEM=PAGEFAULT build (src/cuda/model.cmake:6-10, CUDAStream.cu:39-40,217-221):
+  // the arrays are plain system allocations that the GPUs reach through the page-fault path (HMM or ATS).
+  // Implies `managed` (one range per array, get_arrays returns the ranges); advice and prefetches are
+  // hints only there and a driver that refuses them for system memory is not an error.
+  bool pagefault = false;
 
   // host mirrors for get_arrays
   void* host[3] = {nullptr, nullptr, nullptr};
@@ -293,7 +298,11 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
   if (cmd.kind == CMD_PREFETCH) {
     void* dev[3] = {s->a, s->b, s->c};
     const int dst = cmd.prefetch_to ? cudaCpuDeviceId : s->dev;
-    for (int k = 0; k < 3 && s->count; k++) B200_CUDA(cudaMemPrefetchAsync(dev[k], s->count * eb, dst, s->stream));
+    for (int k = 0; k < 3 && s->count; k++) {
+      const cudaError_t e = cudaMemPrefetchAsync(dev[k], s->count * eb, dst, s->stream);
+      if (e != cudaSuccess && ctx->pagefault) { (void)cudaGetLastError(); break; }  // a hint there: the faults move the pages
+      B200_CUDA(e);
+    }
     B200_CUDA(cudaStreamSynchronize(s->stream));
     return B200_OK;
   }
@@ -384,13 +393,15 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
   } else if (key == "timing") {
     ctx->timing = (val == "1" || val == "on" || val == "true");
   } else if (key == "mem") {
-    const bool want = val == "managed";
-    if (!want && val != "device" && val != "default") { set_error("mem must be device or managed, got '%s'", val.c_str()); return B200_EINVAL; }
-    if (ctx->created && want != ctx->managed) {
+    const bool pf = val == "pagefault";
+    const bool want = val == "managed" || pf;
+    if (!want && val != "device" && val != "default") { set_error("mem must be device, managed or pagefault, got '%s'", val.c_str()); return B200_EINVAL; }
+    if (ctx->created && (want != ctx->managed || pf != ctx->pagefault)) {
       set_error("mem is fixed when the arrays are allocated: pass it to b200_create_opts or set BABELSTREAM_B200_MEM");
       return B200_EINVAL;
     }
     ctx->managed = want;
+    ctx->pagefault = pf;
   } else if (key == "sync") {
     ctx->sync_mode = val == "spin" ? SYNC_SPIN : val == "stream" ? SYNC_STREAM : val == "doorbell" ? SYNC_DOORBELL : SYNC_AUTO;
   } else if (key == "tune") {
@@ -535,7 +546,7 @@ void b200_destroy(b200_ctx* ctx) {
     if (s->dot_host) cudaFreeHost(s->dot_host);
     delete s;
   }
-  for (void* p : ctx->managed_base) if (p) cudaFree(p);
+  for (void* p : ctx->managed_base) if (p) { if (ctx->pagefault) free(p); else cudaFree(p); }
   free_host_mirrors(ctx);
   if (!ctx->shards.empty()) cudaSetDevice(ctx->first_device);
   delete ctx;
@@ -591,8 +602,27 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
 
   // mem=managed: the three arrays are single managed ranges; shard boundaries move to 2 MiB multiples
   // (the managed page size) so that no page is shared by two GPUs
+  // (mem=pagefault: the same, on 2 MiB huge-page boundaries)
   const size_t shard_align = (ctx->managed && ngpus > 1 && n * (size_t)elem_bytes / (size_t)ngpus >= (8u << 20)) ? (2u << 20) : 128;
-  if (ctx->managed) {
+  if (ctx->pagefault) {
+    // "p = (T*)malloc(array_bytes)" (CUDAStream.cu:39-40).  Every GPU that holds a shard must be able to
+    // touch pageable memory; 2 MiB alignment so that shard boundaries fall on (huge) page boundaries.
+    for (int g = 0; g < ngpus; g++) {
+      int pageable = 0;
+      cudaDeviceGetAttribute(&pageable, cudaDevAttrPageableMemoryAccess, first_device + g);
+      if (!pageable) {
+        set_error("mem=pagefault needs GPU access to pageable system memory (HMM or ATS), which device %d does not offer", first_device + g);
+        return fail(B200_EUNSUPPORTED);
+      }
+    }
+    const size_t huge = (size_t)2 << 20;
+    const size_t array_bytes = ((n ? n * (size_t)elem_bytes : 256) + huge - 1) / huge * huge;
+    for (int k = 0; k < 3; k++) {
+      void* p = nullptr;
+      if (posix_memalign(&p, huge, array_bytes) != 0 || !p) { set_error("out of host memory: %zu bytes for a pagefault array", array_bytes); return fail(B200_ENOMEM); }
+      ctx->managed_base[k] = p;
+    }
+  } else if (ctx->managed) {
     int dev0_managed = 0;
     cudaDeviceGetAttribute(&dev0_managed, cudaDevAttrConcurrentManagedAccess, first_device);
     if (!dev0_managed) { set_error("mem=managed needs concurrent managed access, which device %d does not offer", first_device); return fail(B200_EUNSUPPORTED); }
@@ -635,6 +665,12 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
       for (int k = 0; k < 3; k++) {
         *mine[k] = static_cast<char*>(ctx->managed_base[k]) + s->begin * (size_t)elem_bytes;
         if (!shard_bytes) continue;
+        if (ctx->pagefault) {
+          // hints: the pages are not populated yet, init_arrays first-touches them from the owning GPU
+          (void)cudaMemAdvise(*mine[k], shard_bytes, cudaMemAdviseSetPreferredLocation, s->dev);
+          (void)cudaGetLastError();
+          continue;
+        }
         cu(cudaMemAdvise(*mine[k], shard_bytes, cudaMemAdviseSetPreferredLocation, s->dev), "cudaMemAdvise(preferred location)");
         cu(cudaMemPrefetchAsync(*mine[k], shard_bytes, s->dev, s->stream), "cudaMemPrefetchAsync");
       }
@@ -700,7 +736,8 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
   snprintf(line, sizeof line, "GPUs: %d (devices %d..%d), %zu elements of %d bytes, shard %zu elements\n", ctx->ngpus,
            ctx->first_device, ctx->first_device + ctx->ngpus - 1, ctx->n, ctx->elem_bytes, ctx->shards[0]->count);
   out += line;
-  if (ctx->managed) out += "  memory: MANAGED (one cudaMallocManaged range per array, preferred location = owning GPU, prefetched; get_arrays returns the ranges)\n";
+  if (ctx->pagefault) out += "  memory: PAGEFAULT (one system allocation per array, reached by the GPUs through page faults; get_arrays returns the ranges)\n";
+  else if (ctx->managed) out += "  memory: MANAGED (one cudaMallocManaged range per array, preferred location = owning GPU, prefetched; get_arrays returns the ranges)\n";
   const char* names[B200_NUM_KERNELS] = {"copy", "mul", "add", "triad", "nstream", "dot", "init"};
   for (int k = 0; k < B200_NUM_KERNELS; k++) {
     Resolved r;

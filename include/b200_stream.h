@@ -198,7 +198,7 @@ typedef struct b200_ctx b200_ctx;
 b200_ctx* b200_create(int first_device, int ngpus, size_t n, int elem_bytes, int* status);
 /* Same, with options applied BEFORE the arrays are allocated: `options` is a NULL-terminated array of
  * "key=value" strings (keys of b200_set_option) or NULL; they override the environment.  The only way
- * besides BABELSTREAM_B200_MEM to select mem=managed. */
+ * besides BABELSTREAM_B200_MEM to select mem=managed or mem=pagefault. */
 b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes, const char* const* options,
                            int* status);
 void b200_destroy(b200_ctx* ctx);
@@ -218,10 +218,13 @@ int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes);
  * every pair of GPUs has peer access, else nccl), timing=0|1,
  * sync=auto|stream|spin|doorbell (how a blocking call waits: cudaStreamSynchronize | cudaStreamQuery loop |
  * the kernel rings a host flag, see b200_doorbell; auto = doorbell for dot, cudaStreamSynchronize for the rest),
- * mem=device|managed (allocation time only: b200_create_opts or the environment; managed = the reference's
+ * mem=device|managed|pagefault (allocation time only: b200_create_opts or the environment; managed = the reference's
  * MEM=MANAGED build, src/cuda/model.cmake:6-10: one cudaMallocManaged range per array, each shard's
  * preferred location its GPU, shard boundaries on 2 MiB; b200_get_arrays then returns the ranges themselves
- * after prefetching them to the CPU, "Unified memory: return pointers to device memory" CUDAStream.cu:217-221),
+ * after prefetching them to the CPU, "Unified memory: return pointers to device memory" CUDAStream.cu:217-221;
+ * pagefault = the reference's MEM=PAGEFAULT build, CUDAStream.cu:39-40: one 2 MiB-aligned system allocation
+ * per array that the GPUs reach through page faults (HMM/ATS); B200_EUNSUPPORTED where
+ * cudaDevAttrPageableMemoryAccess is 0),
  * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk) */
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
 int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */

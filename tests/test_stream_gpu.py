@@ -194,6 +194,40 @@ def test_managed_memory_mode(orc, dtype):
         bs.B200Stream(16, nonsense="1")
 
 
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_pagefault_memory_mode(orc, dtype):
+    """mem=pagefault (the reference's MEM=PAGEFAULT build, src/cuda/CUDAStream.cu:39-40,217-221): plain system
+    allocations reached by the GPU through page faults.  Same bits as mem=device; get_arrays returns the ranges.
+    Where the device cannot touch pageable memory the constructor must refuse (no silent fallback)."""
+    u = np.uint64 if dtype is np.float64 else np.uint32
+    try:
+        probe = bs.B200Stream(1000, dtype=dtype, mem="pagefault")
+    except bs.B200Error as e:
+        assert e.code == -6 and "pageable" in str(e)     # B200_EUNSUPPORTED
+        pytest.skip("device has no pageable memory access (no HMM/ATS on this box)")
+    probe.close()
+    for n in (1000, (1 << 21) + 17):
+        with bs.B200Stream(n, dtype=dtype, mem="pagefault") as s:
+            assert "PAGEFAULT" in s.describe()
+            total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)
+            a, b, c = s.get_arrays()
+            g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, 3, n)
+            for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+                assert (arr.view(u) == np.asarray(gold).view(u)).all(), n
+            assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, total) == 0
+            a2, _, _ = s.get_arrays()
+            assert a2.ctypes.data == a.ctypes.data and a.ctypes.data % (2 << 20) == 0
+            drive(s, orc, O.ALL, O.ORDER_CLASSIC, 2)      # the CPU touched the pages: the kernels fault them back
+            a, b, c = s.get_arrays()
+            g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, 5, n)
+            for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+                assert (arr.view(u) == np.asarray(gold).view(u)).all(), n
+            ra, _, rc = s.read_arrays()
+            assert np.array_equal(ra.view(u), a.view(u)) and np.array_equal(rc.view(u), c.view(u))
+            with pytest.raises(bs.B200Error):
+                s.set_option("mem", "managed")
+
+
 def test_constructor_errors():
     with pytest.raises(bs.B200Error) as e:
         bs.B200Stream(1024, device=99)
@@ -243,6 +277,17 @@ def test_driver_managed_memory():
     p = run_bin("-s", str((1 << 22) + 3), "-n", "10", "--only", "All", env={"BABELSTREAM_B200_MEM": "managed"})
     assert p.returncode == 0, p.stdout + p.stderr
     assert "MANAGED" in p.stdout
+
+
+@needs_bin
+def test_driver_pagefault_memory_or_loud_refusal():
+    """BABELSTREAM_B200_MEM=pagefault: validates like any other run where the GPU can touch pageable memory,
+    otherwise the constructor throws (the reference's convention, CUDAStream.cu:87-88) -- never a fallback."""
+    p = run_bin("-s", str((1 << 21) + 3), "-n", "10", "--only", "All", env={"BABELSTREAM_B200_MEM": "pagefault"})
+    if p.returncode == 0:
+        assert "PAGEFAULT" in p.stdout
+    else:
+        assert "mem=pagefault needs GPU access to pageable system memory" in p.stderr, p.stdout + p.stderr
 
 
 @needs_bin
