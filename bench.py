@@ -163,8 +163,11 @@ def main_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": 1, "ms_per_step": round(t * 1e3, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"omp-stream fp64 2^{LOG2N} elements, all six kernels, host CPU cores",
-                       "elements": n, "kernels": KERNEL_ORDER},
+            "config": {"workload": f"BabelStream fp64, 2^{LOG2N} elements per GPU, all six kernels (copy mul add triad dot nstream)",
+                       "elements_per_gpu": n, "elements_total": n * args.gpus, "kernels": KERNEL_ORDER,
+                       "bytes_per_step_per_gpu": STEP_WEIGHT * 8 * n,
+                       "run_as": f"reference omp-stream (unmodified sources) on the host CPU cores; each step is a bounded sample "
+                                 f"of the workload: one pass of the six kernels over 2^{LOG2N} fp64 elements"},
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -428,7 +431,7 @@ def main():
         "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"b200-stream fp64, 2^{args.log2n} elements per GPU, all six kernels (copy mul add triad dot nstream)",
+        "config": {"workload": f"BabelStream fp64, 2^{args.log2n} elements per GPU, all six kernels (copy mul add triad dot nstream)",
                    "elements_per_gpu": n, "elements_total": n * world, "kernels": KERNEL_ORDER,
                    "bytes_per_step_per_gpu": step_bytes,
                    "l2": f"inputs larger than L2: 3 arrays x {n * eb / 1e6:.0f} MB per GPU vs 126 MB L2, no flush needed",
