@@ -153,6 +153,51 @@ def test_bench_csv_parser_and_step_metric():
     assert bench.KERNEL_ORDER == bs.KERNELS
 
 
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "omp-stream")), reason="oracle/_ref not built")
+def test_bench_reference_arm_prints_one_contract_line():
+    """`bench.py --impl reference`: the reference's own omp-stream on the host cores, one JSON line with the
+    same metric / unit / config keys as the b200 arm (the driver computes the ratio itself)."""
+    import json
+    import subprocess
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert p.returncode == 0, p.stderr
+    lines = [l for l in p.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    sys.path.insert(0, ROOT)
+    import bench
+    assert d["impl"] == "reference" and d["metric"] == bench.METRIC and d["unit"] == bench.UNIT and d["higher_is_better"] is True
+    assert d["n_gpus"] == 1 and d["steps"] == 2 and d["dtype"] == "f64" and d["vs_baseline"] is None
+    assert d["config"]["elements_per_gpu"] == 1 << bench.LOG2N and d["config"]["kernels"] == bench.KERNEL_ORDER
+    assert d["config"]["bytes_per_step_per_gpu"] == 16 * 8 * (1 << bench.LOG2N)
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["value"] == d["value"] > 0 and "omp-stream" in cb["sample"]
+    assert d["e2e"] == {"value": d["value"], "unit": bench.UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    # value = algorithmic bytes of a step / time of a step
+    assert abs(d["value"] - 16 * 8 * (1 << bench.LOG2N) / (d["ms_per_step"] * 1e-3) / 1e9) < 0.05 * d["value"]
+
+
+def test_report_tool_renders_sweep_csv(tmp_path):
+    """tools/report.py: size-sweep CSV -> markdown with the L2 knee marked and a sample block in
+    the layout of the reference's results/ files."""
+    import subprocess
+    rows = ["model,dtype,log2n,kernel,gbs,min_us,l2_resident"]
+    for model, scale in (("b200", 1.0), ("ref_cuda", 0.8)):
+        for l, res in ((22, 1), (23, 0), (24, 0)):
+            for k, g in (("copy", 6000), ("mul", 6000), ("add", 6500), ("triad", 6600), ("dot", 6400), ("nstream", 7000)):
+                rows.append(f"{model},f64,{l},{k},{g * scale},{100.0},{res}")
+    f = tmp_path / "sweep.csv"
+    f.write_text("\n".join(rows) + "\n")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "report.py"), str(f)], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    out = p.stdout
+    assert "| 22 | L2 |" in out and "| 23 | **knee -> HBM** |" in out and "| 24 | HBM |" in out
+    assert "6600 / 5280 (1.25)" in out                       # triad b200 / ref (ratio)
+    assert f"{100 * 6600 / 8000:.1f} / {100 * 6600 / 7672.3:.1f}" in out
+    assert "Function    MBytes/sec  Min (sec)" in out and "Triad       6600000.000 0.00010" in out
+
+
 # ---- N > 1 on CPU: world_size 2, gloo -----------------------------------------------------------------
 def _free_port():
     with socket.socket() as s:
