@@ -28,7 +28,7 @@ SRCS := $(wildcard $(CSRC)/*.cu)
 OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(SRCS))
 HDRS := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) include/b200_stream.h
 
-.PHONY: all lib driver oracle clean ptxas probe
+.PHONY: all lib driver oracle clean ptxas probe lab
 all: lib oracle driver
 
 lib: $(LIB)
@@ -80,3 +80,9 @@ ptxas:
 
 clean:
 	rm -rf build $(LIB)
+
+# tools/lab/ew_lab: experimental bench of elementwise-kernel candidates (not part of the product)
+lab: build/ew_lab
+build/ew_lab: tools/lab/ew_lab.cu
+	@mkdir -p build
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -ccbin $(HOSTCXX) --threads 0 -o $@ $<

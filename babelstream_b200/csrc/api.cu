@@ -1,5 +1,6 @@
 // api.cu -- LEVEL 0 (queries) and LEVEL 1 (raw launchers) of include/b200_stream.h.
 #include <atomic>
+#include <dlfcn.h>
 #include <limits.h>
 #include <mutex>
 #include <stdio.h>
@@ -11,7 +12,10 @@
 namespace b200 {
 
 static std::atomic<uint64_t> g_launches{0};
-void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+static thread_local uint64_t t_launches = 0;
+void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); t_launches += n; }
+void uncount_launch(unsigned n) { g_launches.fetch_sub(n, std::memory_order_relaxed); t_launches -= n; }
+uint64_t thread_launch_count() { return t_launches; }
 
 int cuda_fail(cudaError_t e, const char* expr, const char* file, int line) {
   // same information as the reference's CU() macro prints (src/cuda/CUDAStream.cu:14-17)
@@ -78,6 +82,29 @@ int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, d
   if (int rc = check_bell(bell, true)) return rc;
   const bool need_a = kernel != B200_MUL, need_b = kernel != B200_COPY, need_c = true;  // which arrays the op touches
   if (n > 0 && ((need_a && !a) || (need_b && !b) || (need_c && !c))) { set_error("null array pointer"); return B200_EINVAL; }
+  // No-alias rule: the array a kernel writes must not overlap an array it reads through the read-only
+  // (ld.global.nc) path -- an in-place call such as triad(a, a, c) would read, non-coherently, memory the same
+  // grid is writing.  (nstream's a is read and written by design and is loaded coherently.)
+  if (n > 0) {
+    const size_t bytes = n * (size_t)elem_bytes;
+    const char* out = static_cast<const char*>(kernel == B200_MUL ? b : (kernel == B200_COPY || kernel == B200_ADD) ? c : a);
+    const void* ins[3] = {(kernel == B200_COPY || kernel == B200_ADD) ? a : nullptr,
+                          (kernel == B200_ADD || kernel == B200_TRIAD || kernel == B200_NSTREAM) ? b : nullptr,
+                          (kernel == B200_MUL || kernel == B200_TRIAD || kernel == B200_NSTREAM) ? c : nullptr};
+    for (const void* in : ins) {
+      const char* r = static_cast<const char*>(in);
+      if (r && kernel != B200_INIT && r < out + bytes && out < r + bytes) {
+        set_error("the array a kernel writes must not overlap the arrays it reads (in-place calls are not supported)");
+        return B200_EINVAL;
+      }
+    }
+    if (kernel == B200_INIT) {
+      const char* p[3] = {static_cast<const char*>(a), static_cast<const char*>(b), static_cast<const char*>(c)};
+      for (int i = 0; i < 3; i++)
+        for (int j = i + 1; j < 3; j++)
+          if (p[i] < p[j] + bytes && p[j] < p[i] + bytes) { set_error("init: the three arrays must not overlap"); return B200_EINVAL; }
+    }
+  }
   const DeviceProps* props = current_device_props(nullptr);
   if (!props) return B200_ENODEVICE;
   EwCall call;
@@ -118,9 +145,12 @@ int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, d
 
 int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
                       void* result_host_mapped, int world, int rank, unsigned long long seq, void* const* mailboxes,
-                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream, bool send_only) {
+                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream, bool send_only, void* status_host,
+                      void* seq_counters) {
   if (int rc = check_common(n, elem_bytes)) return rc;
-  if (int rc = check_bell(bell, false)) return rc;
+  if (bell && seq_counters) {
+    if (!bell->flag_host_mapped) { set_error("doorbell needs a flag address"); return B200_EINVAL; }
+  } else if (int rc = check_bell(bell, false)) return rc;
   if (!workspace || (n > 0 && (!a || !b))) { set_error("b200_launch_dot: null pointer"); return B200_EINVAL; }
   const DeviceProps* props = current_device_props(nullptr);
   if (!props) return B200_ENODEVICE;
@@ -130,6 +160,8 @@ int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, vo
   call.workspace = workspace; call.result_dev = result_dev; call.result_host = result_host_mapped;
   call.p2p_world = world; call.p2p_rank = rank; call.p2p_seq = seq; call.p2p_mailboxes = mailboxes;
   call.p2p_send_only = send_only;
+  call.status_host = status_host;
+  call.seq_counters = seq_counters;
   if (bell) { call.bell.flag = bell->flag_host_mapped; call.bell.seq = bell->seq; }
   call.stream = static_cast<cudaStream_t>(stream);
   call.g = make_geometry(a, b, nullptr, n, elem_bytes, call.r.vec_bytes, call.r.block, call.r.unroll, call.r.cache_hint);
@@ -185,6 +217,37 @@ int b200_device_info(int device, int* num_sms, int* cc_major, int* cc_minor, siz
     *total_mem = p.totalGlobalMem;
   }
   return B200_OK;
+}
+
+int b200_device_ecc(int device) {
+  int v = 0;
+  B200_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrEccEnabled, device));
+  return v ? 1 : 0;
+}
+
+// The reference's banner prints NVML's CURRENT memory clock (src/cuda/CUDAStream.cu:96-108), not the attribute's
+// maximum.  NVML is resolved at run time; without it the attribute value is returned.
+int b200_device_mem_clock_mhz(int device) {
+  int khz = 0;
+  B200_CUDA(cudaDeviceGetAttribute(&khz, cudaDevAttrMemoryClockRate, device));
+  int mhz = khz / 1000;
+  static void* nvml = dlopen("libnvidia-ml.so.1", RTLD_NOW | RTLD_LOCAL);
+  if (nvml) {
+    typedef int (*InitFn)(void);
+    typedef int (*ByBusFn)(const char*, void**);
+    typedef int (*ClockFn)(void*, int, unsigned int*);
+    static InitFn init = (InitFn)dlsym(nvml, "nvmlInit_v2");
+    static ByBusFn by_bus = (ByBusFn)dlsym(nvml, "nvmlDeviceGetHandleByPciBusId_v2");
+    static ClockFn clock = (ClockFn)dlsym(nvml, "nvmlDeviceGetClockInfo");
+    char bus[32];
+    void* dev = nullptr;
+    unsigned int mem = 0;
+    if (init && by_bus && clock && cudaDeviceGetPCIBusId(bus, (int)sizeof bus, device) == cudaSuccess && init() == 0 &&
+        by_bus(bus, &dev) == 0 && clock(dev, /*NVML_CLOCK_MEM*/ 2, &mem) == 0 && mem > 0)
+      mhz = (int)mem;
+    (void)cudaGetLastError();
+  }
+  return mhz;
 }
 
 int b200_launch_init(void* a, void* b, void* c, size_t n, int elem_bytes, double ia, double ib, double ic,
@@ -255,11 +318,20 @@ int b200_launch_dot_send_p2p(const void* a, const void* b, size_t n, int elem_by
 }
 
 int b200_launch_dot_collect_p2p(int elem_bytes, void* result_dev, void* result_host_mapped, int world, int rank,
-                                unsigned long long seq, void* const* mailboxes, void* stream) {
+                                unsigned long long seq, void* const* mailboxes, void* workspace, int flags, void* stream) {
   if (int rc = check_common(0, elem_bytes)) return rc;
   if (!current_device_props(nullptr)) return B200_ENODEVICE;
-  return launch_dot_collect(elem_bytes, result_dev, result_host_mapped, world, rank, seq, mailboxes,
+  void* status = workspace ? static_cast<char*>(workspace) + kDotWsStatus : nullptr;
+  return launch_dot_collect(elem_bytes, result_dev, result_host_mapped, world, rank, seq, mailboxes, status, flags,
                             static_cast<cudaStream_t>(stream));
+}
+
+size_t b200_dot_status_offset(void) { return kDotWsStatus; }
+
+int b200_set_p2p_timeout_ms(double ms) {
+  if (!(ms > 0)) { set_error("b200_set_p2p_timeout_ms: the timeout must be positive"); return B200_EINVAL; }
+  set_p2p_timeout_ns((unsigned long long)(ms * 1e6));
+  return B200_OK;
 }
 
 // ---- cross-process peer memory (one process per GPU) ------------------------------------------

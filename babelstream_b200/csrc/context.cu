@@ -3,9 +3,14 @@
 // Three device-resident arrays of n elements, sharded contiguously over G GPUs of one box
 // (b200_shard_range).  Every public call is blocking, as src/Stream.h:36 demands.
 //   G == 1 : the caller's thread launches and waits; no helper threads at all.
-//   G  > 1 : one pinned worker thread per GPU, released by a shared sequence number and joined by
-//            spinning on per-worker counters, so that the G launches start together instead of
-//            one after another from a single thread (SURVEY.md section 7 "launch skew").
+//   G  > 1 : one worker thread per GPU, released by a shared sequence number and joined through ONE
+//            completion counter, so that the G launches start together instead of one after another
+//            from a single thread (SURVEY.md section 7 "launch skew").
+// Every kernel call replays a one-node CUDA graph that was captured the first time the call was made
+// with these arguments (a "plan"): the arrays, the shape and the scalar never change between the calls
+// of a benchmark run, and cudaGraphLaunch + cudaStreamSynchronize returns 2.0-2.5 us sooner than
+// <<<>>> + cudaStreamSynchronize on B200 at every size (profiles/r02/lab_path.txt).  dot's per-call
+// sequence numbers live in device memory for the same reason.
 // The elementwise kernels never communicate.  dot is the one exchange step: each GPU reduces its
 // shard to one T, and the G values are combined inside the dot kernel by peer stores over NVLink
 // (dot_combine=p2p, the default when every GPU pair has peer access), by ONE ncclAllReduce of
@@ -82,10 +87,21 @@ struct Shard {
   void *a = nullptr, *b = nullptr, *c = nullptr;
   void* dot_ws = nullptr;        // partials + ticket
   void* dot_dev = nullptr;       // 2 x 8 bytes: [0] this GPU's partial, [1] all-reduced value
-  void* dot_host = nullptr;      // mapped pinned, 64 bytes: [0,8) dot's sum, [8,16) the doorbell flag
+  void* dot_host = nullptr;      // mapped pinned, 64 bytes: [0,8) dot's sum, [8,16) dot's doorbell flag,
+                                 // [16,24) the elementwise kernels' doorbell flag, [32,36) all-reduce timeout status
   void* dot_host_dev = nullptr;  // device-side alias of dot_host
   void* bell_ticket = nullptr;   // device word of the elementwise kernels' doorbell
-  unsigned long long bell_seq = 0;
+  unsigned long long bell_seq = 0;      // last value the elementwise doorbell was asked to ring with
+  void* seq_counters = nullptr;  // device, 2 x 8 bytes: dot's doorbell value and all-reduce sequence number (bumped by the kernel)
+  unsigned long long dot_bell_seq = 0;  // host mirror of seq_counters[0]
+  struct Plan {                  // one captured launch, replayed while its key matches
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    double s0 = 0, s1 = 0, s2 = 0;
+    uint64_t gen = 0;            // ctx->tune_gen it was built under
+    unsigned nlaunch = 0;        // kernel nodes (for b200_launch_count)
+    bool bell = false;           // dot: built with the doorbell
+  } plans[B200_NUM_KERNELS];
   void* mailbox = nullptr;       // p2p combine: kMaxPeers slots in this GPU's HBM, written by the peers
   int rank = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -93,14 +109,12 @@ struct Shard {
   float last_ms = -1.f;
   int status = B200_OK;
   std::string error;
-  std::atomic<uint64_t> done{0};
 };
 
 struct Command {
   int kind = CMD_NONE;
   int kernel = 0;
   double s0 = 0, s1 = 0, s2 = 0;
-  unsigned long long seq = 0;                   // dot: sequence number of the p2p all-reduce
   void* host[3] = {nullptr, nullptr, nullptr};  // read: destinations; write: sources
   int prefetch_to = 0;                          // CMD_PREFETCH: 0 = the shard's GPU, 1 = the CPU
 };
@@ -120,6 +134,9 @@ struct b200_ctx {
   bool timing = false;
   bool created = false;  // b200_create finished: the allocation-time options are frozen
   int sync_mode = SYNC_AUTO;
+  int caller_device = -1;    // the device that was current when b200_create was called; restored by create and destroy
+  bool use_graphs = true;    // option launch=graph|direct
+  uint64_t tune_gen = 1;     // bumped by every option change: invalidates the cached plans
   // one process per GPU (b200_join_group): this context is rank group_rank of group_world
   int group_world = 1, group_rank = 0;
   void* group_mailboxes[kMaxPeers] = {};
@@ -128,7 +145,6 @@ struct b200_ctx {
   bool nccl_ready = false;
   bool p2p_ready = false;
   void* mailboxes[kMaxPeers] = {};
-  unsigned long long dot_seq = 0;
 
   // mem=managed: the reference's MEM=MANAGED build (src/cuda/model.cmake:6-10, CUDAStream.cu:37-38,217-221).
   // One cudaMallocManaged range per array; every shard is a sub-range whose preferred location is its
@@ -156,6 +172,7 @@ struct b200_ctx {
   std::vector<std::thread> workers;
   Command cmd;
   std::atomic<uint64_t> seq{0};
+  std::atomic<uint64_t> done_total{0};  // every worker adds 1 per finished command
   std::atomic<int> sleepers{0};
   std::mutex mu;
   std::condition_variable cv;
@@ -179,8 +196,8 @@ static int stream_wait(b200_ctx* ctx, Shard* s) {
 // Wait for the doorbell of the launch just issued (kernels.cuh): spin on the host word the kernel's
 // last block writes.  Every 64 Ki polls the stream is queried, so that a failed launch or a faulting
 // kernel ends in an error instead of a hang.
-static int bell_wait(Shard* s, unsigned long long seq) {
-  const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(static_cast<char*>(s->dot_host) + 8);
+static int bell_wait(Shard* s, unsigned long long seq, int flag_offset) {
+  const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(static_cast<char*>(s->dot_host) + flag_offset);
   for (unsigned spins = 1;; ++spins) {
     if (__atomic_load_n(flag, __ATOMIC_ACQUIRE) == seq) return B200_OK;
     if ((spins & 0xffffu) == 0) {
@@ -216,15 +233,16 @@ static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd, const b200_
   void* st = s->stream;
   if (cmd.kernel == B200_DOT) {
     const bool single = ctx->ngpus == 1;
+    void* const status = static_cast<char*>(s->dot_host_dev) + 32;
     if (single && ctx->group_world > 1) {
       // one process per GPU: same fused kernel, the peers' mailboxes are IPC mappings
       return launch_dot_common(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, s->dot_host_dev, ctx->group_world,
-                               ctx->group_rank, cmd.seq, ctx->group_mailboxes, cfg, bell, st);
+                               ctx->group_rank, 0, ctx->group_mailboxes, cfg, bell, st, false, status, s->seq_counters);
     }
     if (!single && ctx->combine == COMBINE_P2P) {
       // fused: partial + all-reduce over peer memory in ONE launch; an empty shard still takes part
       return launch_dot_common(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, s->dot_host_dev, ctx->ngpus, s->rank,
-                               cmd.seq, ctx->mailboxes, cfg, bell, st);
+                               0, ctx->mailboxes, cfg, bell, st, false, status, s->seq_counters);
     }
     // single GPU: the kernel writes the sum straight into mapped host memory (zero-copy)
     if (s->count == 0) {
@@ -234,12 +252,41 @@ static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd, const b200_
     }
     const bool to_host = single || ctx->combine == COMBINE_HOST;
     return launch_dot_common(s->a, s->b, s->count, eb, s->dot_ws, s->dot_dev, to_host ? s->dot_host_dev : nullptr, 0, 0, 0,
-                             nullptr, cfg, bell, st);
+                             nullptr, cfg, bell, st, false, nullptr, s->seq_counters);
   }
   if (s->count == 0) return B200_OK;
   if (cmd.kernel < 0 || cmd.kernel >= B200_NUM_KERNELS) { set_error("unknown kernel id %d", cmd.kernel); return B200_EINVAL; }
   // launch_ew ignores the arrays a kernel does not touch
   return launch_ew(cmd.kernel, s->a, s->b, s->c, s->count, eb, cmd.s0, cmd.s1, cmd.s2, cfg, bell, st);
+}
+
+// Is the fused peer-memory all-reduce part of this context's dot?
+static bool dot_is_p2p(const b200_ctx* ctx) {
+  return (ctx->ngpus == 1 && ctx->group_world > 1) || (ctx->ngpus > 1 && ctx->combine == COMBINE_P2P);
+}
+
+// Capture the launch of `cmd` on shard `s` into a one-node graph (a plan).  Nothing is enqueued.
+static int build_plan(b200_ctx* ctx, Shard* s, const Command& cmd, const b200_doorbell* bell, Shard::Plan* p) {
+  if (p->exec) { cudaGraphExecDestroy(p->exec); p->exec = nullptr; }
+  if (p->graph) { cudaGraphDestroy(p->graph); p->graph = nullptr; }
+  const uint64_t before = thread_launch_count();
+  B200_CUDA(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
+  const int rc = shard_launch(ctx, s, cmd, bell);
+  cudaGraph_t graph = nullptr;
+  const cudaError_t e = cudaStreamEndCapture(s->stream, &graph);
+  const unsigned n = (unsigned)(thread_launch_count() - before);
+  uncount_launch(n);  // a capture launches nothing; every replay is counted instead
+  if (rc != B200_OK) { if (graph) cudaGraphDestroy(graph); (void)cudaGetLastError(); return rc; }
+  B200_CUDA(e);
+  if (n == 0) { cudaGraphDestroy(graph); set_error("internal: plan without a kernel"); return B200_ECUDA; }
+  const cudaError_t ie = cudaGraphInstantiate(&p->exec, graph, 0);
+  if (ie != cudaSuccess) { cudaGraphDestroy(graph); p->exec = nullptr; return cuda_fail(ie, "cudaGraphInstantiate", __FILE__, __LINE__); }
+  p->graph = graph;
+  p->s0 = cmd.s0; p->s1 = cmd.s1; p->s2 = cmd.s2;
+  p->gen = ctx->tune_gen;
+  p->nlaunch = n;
+  p->bell = bell != nullptr;
+  return B200_OK;
 }
 
 // Everything one GPU does for one command, including the wait.  Runs on the worker thread of the
@@ -250,21 +297,54 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
   using clk = std::chrono::steady_clock;
   clk::time_point t0, t1, t2;
   if (ctx->hostprof) t0 = clk::now();
-  // G == 1 runs on the caller's thread, whose current device may have been changed since create
-  if (ctx->ngpus == 1) B200_CUDA(cudaSetDevice(s->dev));
+  // G == 1 runs on the caller's thread: make the shard's device current for the call and hand the caller's
+  // device back afterwards (the workers of G > 1 own their device for life)
+  struct DeviceScope {
+    int saved = -1, mine = -1;
+    ~DeviceScope() { if (saved >= 0 && saved != mine) cudaSetDevice(saved); }
+  } scope;
+  if (ctx->ngpus == 1) {
+    scope.mine = s->dev;
+    if (cudaGetDevice(&scope.saved) != cudaSuccess) { (void)cudaGetLastError(); scope.saved = -1; }
+    if (scope.saved != s->dev) B200_CUDA(cudaSetDevice(s->dev));
+  }
   if (cmd.kind == CMD_KERNEL) {
     if (ctx->hostprof) t1 = clk::now();
+    const bool is_dot = cmd.kernel == B200_DOT;
+    const bool nccl_dot = is_dot && ctx->ngpus > 1 && ctx->combine == COMBINE_NCCL;
+    const bool launches = is_dot ? (s->count > 0 || dot_is_p2p(ctx)) : s->count > 0;
     if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev0, s->stream));
     b200_doorbell bell_store, *bell = nullptr;
+    unsigned long long want = 0;
+    int flag_off = 8;
+    if (is_dot && launches) want = ++s->dot_bell_seq;  // the kernel bumps seq_counters[0] on every launch
     if (use_doorbell(ctx, s, cmd.kernel)) {
-      bell_store.ticket = s->bell_ticket;
-      bell_store.flag_host_mapped = static_cast<char*>(s->dot_host_dev) + 8;
-      bell_store.seq = ++s->bell_seq;
+      if (is_dot) {  // value: the device-side counter
+        bell_store.ticket = nullptr;
+        bell_store.flag_host_mapped = static_cast<char*>(s->dot_host_dev) + 8;
+        bell_store.seq = 0;
+      } else {
+        bell_store.ticket = s->bell_ticket;
+        bell_store.flag_host_mapped = static_cast<char*>(s->dot_host_dev) + 16;
+        bell_store.seq = want = ++s->bell_seq;
+        flag_off = 16;
+      }
       bell = &bell_store;
     }
-    if (int rc = shard_launch(ctx, s, cmd, bell)) return rc;
+    // Replay a plan whenever nothing in the parameter block changes from call to call.
+    const bool replay = ctx->use_graphs && launches && !ctx->timing && !nccl_dot && !(bell && !is_dot);
+    if (replay) {
+      Shard::Plan& p = s->plans[cmd.kernel];
+      if (!p.exec || p.gen != ctx->tune_gen || p.s0 != cmd.s0 || p.s1 != cmd.s1 || p.s2 != cmd.s2 || p.bell != (bell != nullptr)) {
+        if (int rc = build_plan(ctx, s, cmd, bell, &p)) return rc;
+      }
+      B200_CUDA(cudaGraphLaunch(p.exec, s->stream));
+      count_launch(p.nlaunch);
+    } else if (int rc = shard_launch(ctx, s, cmd, bell)) {
+      return rc;
+    }
     if (ctx->hostprof) t2 = clk::now();
-    if (cmd.kernel == B200_DOT && ctx->ngpus > 1 && ctx->combine == COMBINE_NCCL) {
+    if (nccl_dot) {
       // the one collective of the whole benchmark: G partial sums -> every GPU holds the total
       char* buf = static_cast<char*>(s->dot_dev);
       ncclResult_t r = ctx->nccl.AllReduce(buf, buf + 8, 1, eb == 8 ? ncclDouble : ncclFloat, ncclSum, s->comm, s->stream);
@@ -272,7 +352,12 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
       if (g == 0) B200_CUDA(cudaMemcpyAsync(s->dot_host, buf + 8, eb, cudaMemcpyDeviceToHost, s->stream));
     }
     if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev1, s->stream));
-    if (int rc = bell ? bell_wait(s, bell->seq) : stream_wait(ctx, s)) return rc;
+    // In-process fused all-reduce: every GPU ends up with the same bits and the caller reads GPU 0's copy, so
+    // only worker 0 has to see the kernel finish; stream order protects whatever the others enqueue next.
+    const bool skip_wait = is_dot && g != 0 && ctx->ngpus > 1 && ctx->combine == COMBINE_P2P && !ctx->timing;
+    if (!skip_wait) {
+      if (int rc = bell ? bell_wait(s, want, flag_off) : stream_wait(ctx, s)) return rc;
+    }
     if (ctx->hostprof && g == 0) {
       const clk::time_point t3 = clk::now();
       ctx->prof_ns[0] += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count();
@@ -281,6 +366,16 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
       ctx->prof_calls++;
     }
     if (ctx->timing) B200_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
+    if (is_dot && !skip_wait && dot_is_p2p(ctx)) {
+      volatile unsigned int* status = reinterpret_cast<volatile unsigned int*>(static_cast<char*>(s->dot_host) + 32);
+      if (*status) {
+        *status = 0;
+        set_error("dot: the peer-memory all-reduce timed out after %.0f ms waiting for another rank's partial sum "
+                  "(rank %d of %d); the result is NaN", (double)p2p_timeout_ns() * 1e-6,
+                  ctx->ngpus > 1 ? s->rank : ctx->group_rank, ctx->ngpus > 1 ? ctx->ngpus : ctx->group_world);
+        return B200_ETIMEOUT;
+      }
+    }
     return B200_OK;
   }
   if (cmd.kind == CMD_READ || cmd.kind == CMD_WRITE) {
@@ -325,11 +420,11 @@ static void worker_main(b200_ctx* ctx, int g) {
     }
     seen++;
     const Command cmd = ctx->cmd;  // published before seq was bumped
-    if (cmd.kind == CMD_QUIT) { s->done.store(seen, std::memory_order_release); return; }
+    if (cmd.kind == CMD_QUIT) { ctx->done_total.fetch_add(1, std::memory_order_release); return; }
     const int rc = shard_execute(ctx, g, cmd);
     s->status = rc;
     if (rc != B200_OK) s->error = b200_last_error();
-    s->done.store(seen, std::memory_order_release);
+    ctx->done_total.fetch_add(1, std::memory_order_release);
   }
 }
 
@@ -342,15 +437,16 @@ static int run_all(b200_ctx* ctx, const Command& cmd) {
     { std::lock_guard<std::mutex> lock(ctx->mu); }
     ctx->cv.notify_all();
   }
-  int rc = B200_OK;
-  for (Shard* s : ctx->shards) {
-    unsigned spins = 0;
-    while (s->done.load(std::memory_order_acquire) < target) {
-      if (++spins < (1u << 20)) B200_PAUSE();
-      else std::this_thread::yield();
-    }
-    if (s->status != B200_OK && rc == B200_OK) { rc = s->status; set_error("GPU %d: %s", s->dev, s->error.c_str()); }
+  // join: ONE counter that every worker bumps once per command (not G flags polled in series)
+  const uint64_t all_done = target * (uint64_t)ctx->ngpus;
+  unsigned spins = 0;
+  while (ctx->done_total.load(std::memory_order_acquire) < all_done) {
+    if (++spins < (1u << 22)) B200_PAUSE();
+    else std::this_thread::yield();
   }
+  int rc = B200_OK;
+  for (Shard* s : ctx->shards)
+    if (s->status != B200_OK && rc == B200_OK) { rc = s->status; set_error("GPU %d: %s", s->dev, s->error.c_str()); }
   return rc;
 }
 
@@ -380,7 +476,11 @@ static int kernel_by_name(const std::string& s) {
 }
 
 static int apply_option(b200_ctx* ctx, const std::string& key, const std::string& val) {
-  if (key == "contract") {
+  ctx->tune_gen++;  // whatever changes: the cached plans are rebuilt on their next use
+  if (key == "launch") {
+    if (val != "graph" && val != "direct") { set_error("launch must be graph or direct, got '%s'", val.c_str()); return B200_EINVAL; }
+    ctx->use_graphs = val == "graph";
+  } else if (key == "contract") {
     const int c = (val == "off" || val == "0" || val == "unfused") ? 2 : 1;
     for (auto& t : ctx->tune) t.contract = c;
   } else if (key == "copy_variant") {
@@ -465,6 +565,11 @@ static int ensure_host_mirrors(b200_ctx* ctx) {
 // Bring up whatever the selected multi-GPU dot combine needs.  Caller's thread, workers idle.
 static int ensure_combine_ready(b200_ctx* ctx) {
   if (ctx->ngpus == 1 || ctx->combine == COMBINE_HOST) return B200_OK;
+  struct DeviceScope {  // the caller's current device is put back on every way out
+    int saved = -1;
+    DeviceScope() { if (cudaGetDevice(&saved) != cudaSuccess) { (void)cudaGetLastError(); saved = -1; } }
+    ~DeviceScope() { if (saved >= 0) cudaSetDevice(saved); }
+  } scope;
   if (ctx->combine == COMBINE_AUTO) {
     // Default: the fused peer-memory all-reduce (one launch, no NCCL bring-up) whenever every pair of
     // GPUs has peer access -- always true on an NVSwitch box -- otherwise one ncclAllReduce.
@@ -487,7 +592,6 @@ static int ensure_combine_ready(b200_ctx* ctx) {
     if (r != ncclSuccess) { set_error("ncclCommInitAll failed: %s", ctx->nccl.GetErrorString(r)); return B200_ENCCL; }
     for (int g = 0; g < ctx->ngpus; g++) ctx->shards[g]->comm = comms[g];
     ctx->nccl_ready = true;
-    cudaSetDevice(ctx->first_device);
     return B200_OK;
   }
   if (ctx->p2p_ready) return B200_OK;
@@ -510,7 +614,6 @@ static int ensure_combine_ready(b200_ctx* ctx) {
     ctx->mailboxes[s->rank] = s->mailbox;
   }
   for (Shard* s : ctx->shards) { B200_CUDA(cudaSetDevice(s->dev)); B200_CUDA(cudaDeviceSynchronize()); }
-  cudaSetDevice(ctx->first_device);
   ctx->p2p_ready = true;
   return B200_OK;
 }
@@ -541,14 +644,18 @@ void b200_destroy(b200_ctx* ctx) {
     if (s->stream) cudaStreamDestroy(s->stream);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    for (auto& p : s->plans) {
+      if (p.exec) cudaGraphExecDestroy(p.exec);
+      if (p.graph) cudaGraphDestroy(p.graph);
+    }
     if (!ctx->managed) { cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); }
-    cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox); cudaFree(s->bell_ticket);
+    cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox); cudaFree(s->bell_ticket); cudaFree(s->seq_counters);
     if (s->dot_host) cudaFreeHost(s->dot_host);
     delete s;
   }
   for (void* p : ctx->managed_base) if (p) { if (ctx->pagefault) free(p); else cudaFree(p); }
   free_host_mirrors(ctx);
-  if (!ctx->shards.empty()) cudaSetDevice(ctx->first_device);
+  if (ctx->caller_device >= 0) cudaSetDevice(ctx->caller_device);
   delete ctx;
 }
 
@@ -582,9 +689,10 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
   if (!ctx) { set_error("out of host memory"); return fail(B200_ENOMEM); }
   ctx->first_device = first_device; ctx->ngpus = ngpus; ctx->n = n; ctx->elem_bytes = elem_bytes;
   memset(ctx->tune, 0, sizeof ctx->tune);
+  if (cudaGetDevice(&ctx->caller_device) != cudaSuccess) { (void)cudaGetLastError(); ctx->caller_device = -1; }
 
   // options from the environment: BABELSTREAM_B200_<KEY>
-  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem"};
+  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem", "launch"};
   for (const char* k : keys) {
     std::string env = "BABELSTREAM_B200_";
     for (const char* p = k; *p; p++) env += (char)toupper(*p);
@@ -644,8 +752,6 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
     auto cu = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && rc == B200_OK) rc = cuda_fail(e, what, __FILE__, __LINE__); };
     cu(cudaSetDevice(s->dev), "cudaSetDevice");
     if (rc) return fail(rc);
-    (void)cudaSetDeviceFlags(cudaDeviceScheduleSpin);  // best effort: blocking calls should not yield the core
-    (void)cudaGetLastError();
     if (!current_device_props(nullptr)) return fail(B200_EUNSUPPORTED);
     size_t free_b = 0, total_b = 0;
     cu(cudaMemGetInfo(&free_b, &total_b), "cudaMemGetInfo");
@@ -682,6 +788,7 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
     cu(cudaMalloc(&s->dot_ws, kDotWorkspaceBytes), "cudaMalloc(dot workspace)");
     cu(cudaMalloc(&s->dot_dev, 16), "cudaMalloc(dot scalars)");
     cu(cudaMalloc(&s->bell_ticket, 256), "cudaMalloc(doorbell ticket)");
+    cu(cudaMalloc(&s->seq_counters, 256), "cudaMalloc(sequence counters)");
     cu(cudaHostAlloc(&s->dot_host, 64, cudaHostAllocMapped | cudaHostAllocPortable), "cudaHostAlloc(dot result)");
     if (rc) return fail(rc);
     memset(s->dot_host, 0, 64);
@@ -689,6 +796,7 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
     cu(cudaMemsetAsync(s->dot_ws, 0, kDotWorkspaceBytes, s->stream), "cudaMemsetAsync");
     cu(cudaMemsetAsync(s->dot_dev, 0, 16, s->stream), "cudaMemsetAsync");
     cu(cudaMemsetAsync(s->bell_ticket, 0, 256, s->stream), "cudaMemsetAsync");
+    cu(cudaMemsetAsync(s->seq_counters, 0, 256, s->stream), "cudaMemsetAsync");
     cu(cudaStreamSynchronize(s->stream), "cudaStreamSynchronize");
     if (rc) return fail(rc);
   }
@@ -698,7 +806,7 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
     if (rc) return fail(rc);
     for (int g = 0; g < ngpus; g++) ctx->workers.emplace_back(worker_main, ctx, g);
   }
-  cudaSetDevice(first_device);
+  cudaSetDevice(ctx->caller_device >= 0 ? ctx->caller_device : first_device);  // the caller's current device is left as it was
   ctx->created = true;
   if (status) *status = B200_OK;
   return ctx;
@@ -723,13 +831,31 @@ int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes) 
   }
   ctx->group_world = world;
   ctx->group_rank = rank;
-  ctx->dot_seq = 0;  // every rank counts its dot calls from the moment it joins
+  ctx->tune_gen++;  // dot's plan changes shape
+  // Every rank counts its dot calls from the moment it joins: the all-reduce sequence number (device counter)
+  // restarts at 0, and this rank's OWN mailbox is wiped so that no {flag, payload} word of an earlier group,
+  // context or LEVEL 1 call can be mistaken for a partial of the new group.  The caller must put a barrier
+  // between the join of all ranks and the first dot (a fast peer's partial must not land before the wipe).
+  Shard* s = ctx->shards[0];
+  int saved = -1;
+  if (cudaGetDevice(&saved) != cudaSuccess) { (void)cudaGetLastError(); saved = -1; }
+  cudaError_t e = cudaSetDevice(s->dev);
+  if (e == cudaSuccess) e = cudaMemsetAsync(static_cast<char*>(s->seq_counters) + 8, 0, 8, s->stream);
+  if (e == cudaSuccess && world > 1) e = cudaMemsetAsync(mailboxes[rank], 0, b200_dot_mailbox_bytes(), s->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+  if (saved >= 0 && saved != s->dev) cudaSetDevice(saved);
+  if (e != cudaSuccess) return cuda_fail(e, "b200_join_group: reset of the sequence counter / own mailbox", __FILE__, __LINE__);
+  *reinterpret_cast<volatile unsigned int*>(static_cast<char*>(s->dot_host) + 32) = 0;
   return B200_OK;
 }
 
 int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
   if (!ctx || !buf || buflen <= 0) { set_error("b200_describe: null argument"); return B200_EINVAL; }
+  int saved = -1;
+  if (cudaGetDevice(&saved) != cudaSuccess) { (void)cudaGetLastError(); saved = -1; }
+  if (saved != ctx->shards[0]->dev) B200_CUDA(cudaSetDevice(ctx->shards[0]->dev));  // describe the context's GPU, not the caller's
   const DeviceProps* props = current_device_props(nullptr);
+  if (saved >= 0 && saved != ctx->shards[0]->dev) cudaSetDevice(saved);
   if (!props) return B200_ENODEVICE;
   std::string out;
   char line[256];
@@ -766,6 +892,8 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
                               "cudaStreamQuery spin", "doorbell"};
   snprintf(line, sizeof line, "  wait: %s\n", sync_names[ctx->sync_mode + 1]);
   out += line;
+  out += ctx->use_graphs ? "  launch: every call replays a captured one-kernel CUDA graph (launch=direct: <<<>>>)\n"
+                         : "  launch: direct (<<<>>> per call)\n";
   snprintf(buf, (size_t)buflen, "%s", out.c_str());
   return B200_OK;
 }
@@ -786,7 +914,6 @@ static int run_kernel(b200_ctx* ctx, int kernel, double s0, double s1, double s2
   if (int rc = managed_home(ctx)) return rc;
   Command cmd;
   cmd.kind = CMD_KERNEL; cmd.kernel = kernel; cmd.s0 = s0; cmd.s1 = s1; cmd.s2 = s2;
-  if (kernel == B200_DOT) cmd.seq = ++ctx->dot_seq;
   return run_all(ctx, cmd);
 }
 
@@ -862,6 +989,7 @@ int b200_get_arrays(b200_ctx* ctx, const void** a, const void** b, const void** 
 }
 
 int b200_num_gpus(b200_ctx* ctx) { return ctx ? ctx->ngpus : B200_EINVAL; }
+const char* b200_memory_mode(b200_ctx* ctx) { return !ctx ? "" : ctx->pagefault ? "PAGEFAULT" : ctx->managed ? "MANAGED" : "DEFAULT"; }
 size_t b200_array_size(b200_ctx* ctx) { return ctx ? ctx->n : 0; }
 int b200_elem_bytes(b200_ctx* ctx) { return ctx ? ctx->elem_bytes : B200_EINVAL; }
 

@@ -1,8 +1,23 @@
 // dot.cu -- launcher for the two dot variants (see kernels.cuh for the algorithm).
+#include <stdlib.h>
+
 #include "internal.h"
 #include "kernels.cuh"
 
 namespace b200 {
+
+// How long the collecting warp of the peer-memory all-reduce waits for a missing peer before it gives up
+// and reports B200_ETIMEOUT: BABELSTREAM_B200_P2P_TIMEOUT_MS (default 2000), b200_set_p2p_timeout_ms().
+static unsigned long long g_p2p_timeout_ns = 0;
+unsigned long long p2p_timeout_ns() {
+  if (g_p2p_timeout_ns == 0) {
+    double ms = 2000.0;
+    if (const char* e = getenv("BABELSTREAM_B200_P2P_TIMEOUT_MS")) { const double v = atof(e); if (v > 0) ms = v; }
+    g_p2p_timeout_ns = (unsigned long long)(ms * 1e6);
+  }
+  return g_p2p_timeout_ns;
+}
+void set_p2p_timeout_ns(unsigned long long ns) { g_p2p_timeout_ns = ns ? ns : 1; }
 
 #define B200_DOT_FOR_HINT(H)                                                                      \
   B200_DOT_CASE(8, 1, H) B200_DOT_CASE(8, 2, H) B200_DOT_CASE(8, 4, H)                            \
@@ -31,23 +46,23 @@ static int launch_dot_typed(const DotCall& call) {
   DotArgs args;
   args.a = call.a; args.b = call.b;
   args.partials = call.workspace;
-  args.ticket = reinterpret_cast<unsigned int*>(static_cast<char*>(call.workspace) + kDotMaxBlocks * 8);
   args.result_dev = call.result_dev; args.result_host = call.result_host;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
   args.bell_flag = static_cast<unsigned long long*>(call.bell.flag); args.bell_seq = call.bell.seq;
+  args.seq_counters = static_cast<unsigned long long*>(call.seq_counters);
   args.p2p.world = call.p2p_world; args.p2p.rank = call.p2p_rank; args.p2p.seq = call.p2p_seq;
+  args.p2p.timeout_ns = p2p_timeout_ns();
+  args.p2p.status_dev = reinterpret_cast<unsigned int*>(static_cast<char*>(call.workspace) + kDotWsStatus);
+  args.p2p.status_host = static_cast<unsigned int*>(call.status_host);
   for (int g = 0; g < kMaxPeers; g++)
     args.p2p.mailbox[g] = (call.p2p_world > 1 && g < call.p2p_world) ? static_cast<MailSlot*>(call.p2p_mailboxes[g]) : nullptr;
-  k<<<call.grid, call.r.block, 0, call.stream>>>(args);
-  count_launch();
-  B200_CUDA(cudaPeekAtLastError());
+  if (int rc = launch_kernel(k, call.grid, call.r.block, 0, call.stream, call.r.flags, args)) return rc;
   if (MODE == DOT_TWO_PASS) {
-    // same block size as pass 1, so that both variants add the partials in the same order
-    dot_final_kernel<T><<<1, call.r.block, 0, call.stream>>>(static_cast<const T*>(call.workspace), call.grid,
-                                                      static_cast<T*>(call.result_dev),
-                                                      static_cast<T*>(call.result_host), args.bell_flag, args.bell_seq);
-    count_launch();
-    B200_CUDA(cudaPeekAtLastError());
+    // one block of 32 warps: warp g adds group g -- the same order as the ticket variant, whatever the grid
+    if (int rc = launch_kernel(dot_final_kernel<T>, 1u, 1024, 0, call.stream, call.r.flags, static_cast<const T*>(call.workspace),
+                               call.grid, static_cast<T*>(call.result_dev), static_cast<T*>(call.result_host), args.bell_flag,
+                               args.bell_seq))
+      return rc;
   }
   return B200_OK;
 }
@@ -57,7 +72,8 @@ int launch_dot_impl(const DotCall& call) {
   const bool ticket = call.r.variant == B200_VARIANT_DOT_TICKET;
   if (call.p2p_world > 1) {
     if (!ticket) { set_error("the fused peer-memory all-reduce needs the ticket variant of dot"); return B200_EINVAL; }
-    if (call.p2p_world > kMaxPeers || call.p2p_rank < 0 || call.p2p_rank >= call.p2p_world || !call.p2p_mailboxes || call.p2p_seq == 0) {
+    if (call.p2p_world > kMaxPeers || call.p2p_rank < 0 || call.p2p_rank >= call.p2p_world || !call.p2p_mailboxes ||
+        (call.p2p_seq == 0 && !call.seq_counters)) {
       set_error("dot p2p: bad world/rank/seq/mailboxes (world %d, rank %d)", call.p2p_world, call.p2p_rank);
       return B200_EINVAL;
     }
@@ -80,7 +96,7 @@ int launch_dot_impl(const DotCall& call) {
 }
 
 int launch_dot_collect(int elem_bytes, void* result_dev, void* result_host, int world, int rank, unsigned long long seq,
-                       void* const* mailboxes, cudaStream_t stream) {
+                       void* const* mailboxes, void* status_dev, int flags, cudaStream_t stream) {
   if (world < 2 || world > kMaxPeers || rank < 0 || rank >= world || !mailboxes || seq == 0) {
     set_error("dot collect: bad world/rank/seq/mailboxes (world %d, rank %d)", world, rank);
     return B200_EINVAL;
@@ -88,14 +104,16 @@ int launch_dot_collect(int elem_bytes, void* result_dev, void* result_host, int 
   P2PArgs p;
   for (int g = 0; g < kMaxPeers; g++) p.mailbox[g] = g < world ? static_cast<MailSlot*>(mailboxes[g]) : nullptr;
   p.seq = seq; p.world = world; p.rank = rank;
+  p.timeout_ns = p2p_timeout_ns();
+  p.status_dev = static_cast<unsigned int*>(status_dev);
+  p.status_host = nullptr;
   if (!p.mailbox[rank]) { set_error("dot collect: own mailbox is null"); return B200_EINVAL; }
+  unsigned long long* const no_bell = nullptr;
   if (elem_bytes == 8)
-    dot_collect_kernel<double><<<1, 32, 0, stream>>>(p, static_cast<double*>(result_dev), static_cast<double*>(result_host), nullptr, 0);
-  else
-    dot_collect_kernel<float><<<1, 32, 0, stream>>>(p, static_cast<float*>(result_dev), static_cast<float*>(result_host), nullptr, 0);
-  count_launch();
-  B200_CUDA(cudaPeekAtLastError());
-  return B200_OK;
+    return launch_kernel(dot_collect_kernel<double>, 1u, 32, 0, stream, flags, p, static_cast<double*>(result_dev),
+                         static_cast<double*>(result_host), no_bell, 0ull);
+  return launch_kernel(dot_collect_kernel<float>, 1u, 32, 0, stream, flags, p, static_cast<float*>(result_dev),
+                       static_cast<float*>(result_host), no_bell, 0ull);
 }
 
 }  // namespace b200

@@ -29,12 +29,46 @@ struct DeviceProps {
 const DeviceProps* current_device_props(int* device_out);
 
 void count_launch(unsigned n = 1);
+void uncount_launch(unsigned n);   // a stream capture "launched" n kernels that never ran
+uint64_t thread_launch_count();    // launches counted on the calling thread
+
+// Every kernel of the library is launched through here.  flags & B200_LAUNCH_PDL adds the
+// programmatic-stream-serialization attribute (see pdl_entry() in kernels.cuh).
+template <typename... KArgs, typename... Args>
+int launch_kernel(void (*kernel)(KArgs...), unsigned grid, int block, size_t smem, cudaStream_t stream, int flags,
+                  Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  if (flags & B200_LAUNCH_PDL) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+  count_launch();
+  if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx", __FILE__, __LINE__);
+  return B200_OK;
+}
+
+// bound of the peer-memory all-reduce's wait for a missing peer (dot.cu)
+unsigned long long p2p_timeout_ns();
+void set_p2p_timeout_ns(unsigned long long ns);
 
 // A fully resolved launch: no "auto" left.
 struct Resolved {
   int vec_bytes, unroll, block, cache_hint, variant, contract, stages, chunk_bytes;
+  int flags;        // B200_LAUNCH_* bits
   int grid_policy;  // the cfg.grid convention: >0 exact, <0 per-SM, INT32_MAX one tile per block
 };
+
+// Size class of a problem: the footprint of the three arrays against the L2 size (tuning.cu)
+enum { SIZE_L2 = 0, SIZE_KNEE = 1, SIZE_HBM = 2, SIZE_HBM_XL = 3 };
+int size_class(size_t n, int elem_bytes, int l2_bytes);
 
 // Fills every auto field of `in` (may be null) for (kernel, n, elem_bytes).  Pure host logic.
 int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
@@ -97,6 +131,8 @@ struct DotCall {
   unsigned long long p2p_seq = 0;
   void* const* p2p_mailboxes = nullptr;
   bool p2p_send_only = false;  // the sending half only; launch_dot_collect sums later
+  void* status_host = nullptr; // mapped pinned word set to 1 when the collect times out (LEVEL 2), or null
+  void* seq_counters = nullptr;// device: [0] doorbell value, [1] all-reduce sequence number, bumped by the kernel (LEVEL 2)
   Bell bell;  // only .flag and .seq are used: dot has its own ticket
   Resolved r;
   Geometry g;
@@ -105,14 +141,15 @@ struct DotCall {
 };
 int launch_dot_impl(const DotCall& call);
 int launch_dot_collect(int elem_bytes, void* result_dev, void* result_host, int world, int rank, unsigned long long seq,
-                       void* const* mailboxes, cudaStream_t stream);
+                       void* const* mailboxes, void* status_dev, int flags, cudaStream_t stream);
 
 // shared bodies of the LEVEL 1 launchers (api.cu), also called by LEVEL 2 with a doorbell
 int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, double s0, double s1, double s2,
               const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream);
 int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
                       void* result_host_mapped, int world, int rank, unsigned long long seq, void* const* mailboxes,
-                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream, bool send_only = false);
+                      const b200_launch_cfg* cfg, const b200_doorbell* bell, void* stream, bool send_only = false,
+                      void* status_host = nullptr, void* seq_counters = nullptr);
 
 int launch_copy_bulk(const void* src, void* dst, size_t bytes, const Resolved& r, const DeviceProps& props,
                      cudaStream_t stream);

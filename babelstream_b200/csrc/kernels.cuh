@@ -189,6 +189,21 @@ __device__ __forceinline__ Words<VB> pack(const Elems<T, VB>& e) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  Every kernel starts with: "the next kernel of this stream may be
+// scheduled as soon as all my blocks have started" and "wait until the previous kernel of the stream
+// has completed and its memory is visible".  Both are no-ops unless the launch carries the
+// programmatic-stream-serialization attribute (cfg.flags & B200_LAUNCH_PDL), in which case the
+// ~1-2 us drain-and-launch gap between consecutive kernels of an asynchronous sequence disappears:
+// the successor's blocks are already resident, parked in griddepcontrol.wait, when the predecessor's
+// last block retires.  A successor can only be scheduled once ALL blocks of its predecessor are
+// running, so it never takes an SM slot a predecessor block is still waiting for.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_entry() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
 // Completion doorbell.  A blocking caller normally learns that a kernel has finished from
 // cudaStreamSynchronize, i.e. from the semaphore the front end releases after the grid has drained
 // and its caches are flushed, plus the driver's own bookkeeping: 2-3 us after the last store.  With
@@ -266,6 +281,7 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
   constexpr bool LB = (OP == OP_ADD || OP == OP_TRIAD || OP == OP_NSTREAM);
   constexpr bool LC = (OP == OP_MUL || OP == OP_TRIAD || OP == OP_NSTREAM);
   constexpr bool A_RO = (OP == OP_COPY || OP == OP_ADD);  // a is read AND written by nstream: no .nc
+  pdl_entry();
 
   T* const a = static_cast<T*>(args.a);
   T* const b = static_cast<T*>(args.b);
@@ -346,13 +362,28 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
 // Dot.  Pass 1: every thread accumulates UNROLL*EPV independent chains over its vectors
 // (FUSED: acc = fma(a,b,acc); else acc = acc + round(a*b)), folds them in a fixed order, then
 // warp shuffle tree -> one shared-memory slot per warp -> warp 0 -> block partial.
-// Pass 2 (deterministic): ONE block adds the gridDim.x partials in a fixed strided order with
-// the same tree.  It runs either as a second launch (dot_final_kernel) or, TICKET = true, inside
-// pass 1 by whichever block finishes last -- the order of the additions does not depend on which
-// block that is, so both give the same bits.
+// Pass 2 (deterministic, two levels): the gridDim.x partials are split into NG = min(32, gridDim.x)
+// interleaved groups (block b belongs to group b % NG).  ONE WARP adds the partials of a group in a fixed
+// order (lane-strided chains, shuffle tree), and one warp adds the NG group sums the same way.
+// It runs either as a second launch (dot_final_kernel: warp g of one block takes group g) or,
+// TICKET = true, inside pass 1: the last block of each group to finish (a ticket per group) adds its
+// group, and whichever of those NG blocks comes last (a second ticket) adds the group sums.  The
+// order of the additions never depends on which block does them, so both variants give the same bits.
+// Why two levels: with one ticket, ~1200 blocks that finish together queue ~1200 atomics on ONE L2
+// address (2-3 ns each) and the winner then needs a whole-block pass over all partials; with groups
+// no address sees more than ~37 atomics and the critical path after the last block's loads is two
+// atomics and two one-warp sums.
 // ------------------------------------------------------------------------------------------------
 constexpr int kDotMaxBlocks = 4096;
-constexpr size_t kDotWorkspaceBytes = kDotMaxBlocks * 8 + 256;  // partials + ticket
+constexpr int kDotGroups = 32;
+constexpr int kDotTicketStride = 64;  // in 32-bit words: every ticket on its own 256-byte line
+// workspace layout in bytes (zero-initialised once by the caller; every launch leaves it zeroed again,
+// except the status word):
+constexpr size_t kDotWsTop = (size_t)kDotMaxBlocks * 8;                         // top-level ticket
+constexpr size_t kDotWsStatus = kDotWsTop + 128;                                // != 0: a peer-memory collect timed out
+constexpr size_t kDotWsGroupSums = kDotWsTop + 256;                             // T[kDotGroups]
+constexpr size_t kDotWsGroupTickets = kDotWsGroupSums + 256;                    // kDotGroups tickets, 256 bytes apart
+constexpr size_t kDotWorkspaceBytes = kDotWsGroupTickets + (size_t)kDotGroups * kDotTicketStride * 4;
 
 template <typename T>
 __device__ __forceinline__ T warp_sum(T v) {
@@ -376,12 +407,21 @@ __device__ __forceinline__ T block_sum(T v, T* scratch) {
   return v;
 }
 
-// valid in thread 0
+__device__ __forceinline__ unsigned dot_num_groups(unsigned nparts) { return nparts < (unsigned)kDotGroups ? nparts : (unsigned)kDotGroups; }
+
+// One full warp adds the partials of group g (partials g, g+ng, g+2ng, ...).  Valid in lane 0.
 template <typename T>
-__device__ __forceinline__ T dot_second_pass(const T* partials, unsigned nparts, T* scratch) {
+__device__ __forceinline__ T dot_group_sum(const T* partials, unsigned nparts, unsigned ng, unsigned g) {
+  const unsigned lane = threadIdx.x & 31u;
   T v = T(0);
-  for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) v = add_rn(v, __ldcg(partials + i));
-  return block_sum(v, scratch);
+  for (unsigned i = g + ng * lane; i < nparts; i += ng * 32u) v = add_rn(v, __ldcg(partials + i));
+  return warp_sum(v);
+}
+// One full warp adds the ng <= 32 group sums.  Valid in lane 0.
+template <typename T>
+__device__ __forceinline__ T dot_top_sum(const T* gsums, unsigned ng) {
+  const unsigned lane = threadIdx.x & 31u;
+  return warp_sum(lane < ng ? __ldcg(gsums + lane) : T(0));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -391,7 +431,8 @@ __device__ __forceinline__ T dot_second_pass(const T* partials, unsigned nparts,
 // over NVLink / NVSwitch),  (2) waits until all G slots of its OWN mailbox carry this call's sequence
 // number,  (3) adds the G values in rank order.  Every GPU ends up with the same bits.  The G kernels
 // run on G different devices at the same time, so the wait cannot deadlock on scheduling; a
-// globaltimer bound turns a missing peer into a NaN result instead of a hang.
+// globaltimer bound (P2PArgs::timeout_ns) turns a missing peer into a NaN result plus a status word
+// that the host checks, instead of a hang.
 //
 // Wire format: every 8-byte word of a slot carries its own flag -- {payload: 32 bits, flag = low 32
 // bits of seq} -- and an aligned 8-byte store is single-copy atomic, so a word is valid exactly when
@@ -428,6 +469,9 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 struct P2PArgs {
   MailSlot* mailbox[kMaxPeers];  // mailbox[g] = GPU g's mailbox as seen from THIS device
   unsigned long long seq;        // strictly increasing per dot call, equal on all GPUs
+  unsigned long long timeout_ns; // how long the collecting warp waits for a peer before it gives up
+  unsigned int* status_dev;      // device word, set to 1 when the wait timed out (never cleared by a kernel)
+  unsigned int* status_host;     // same, mapped pinned host memory; may be null
   int world;                     // 0 or 1: no exchange
   int rank;
 };
@@ -444,12 +488,12 @@ template <> __device__ __forceinline__ float from_bits<float>(unsigned long long
 // whatever runs in between.
 // send: lanes < world of one warp store {bits, seq} into slot `rank` of every GPU's mailbox.
 template <typename T>
-__device__ __forceinline__ void p2p_send_warp(const P2PArgs& p, T mine) {
+__device__ __forceinline__ void p2p_send_warp(const P2PArgs& p, T mine, unsigned long long seq) {
   const int lane = threadIdx.x & 31;
-  const int bank = (int)(p.seq & 1ull) * kMaxPeers;
+  const int bank = (int)(seq & 1ull) * kMaxPeers;
   if (lane < p.world) {
     MailSlot* dst = p.mailbox[lane] + bank + p.rank;   // my slot in GPU `lane`'s mailbox
-    const unsigned long long bits = to_bits<T>(mine), flag = (p.seq & 0xffffffffull) << 32;
+    const unsigned long long bits = to_bits<T>(mine), flag = (seq & 0xffffffffull) << 32;
     st_relaxed_sys(&dst->w[0], flag | (bits & 0xffffffffull));
     if constexpr (sizeof(T) == 8) st_relaxed_sys(&dst->w[1], flag | (bits >> 32));
   }
@@ -457,27 +501,35 @@ __device__ __forceinline__ void p2p_send_warp(const P2PArgs& p, T mine) {
 // collect: one full warp waits for the `world` slots of its OWN mailbox (local HBM) to carry p.seq and
 // adds them in rank order; the sum (identical on every GPU) is returned in every lane.
 template <typename T>
-__device__ __forceinline__ T p2p_collect_warp(const P2PArgs& p) {
+__device__ __forceinline__ T p2p_collect_warp(const P2PArgs& p, unsigned long long seq) {
   const int lane = threadIdx.x & 31;
-  const int bank = (int)(p.seq & 1ull) * kMaxPeers;
+  const int bank = (int)(seq & 1ull) * kMaxPeers;
   bool ok = true;
   T got = T(0);
   if (lane < p.world) {
     const MailSlot* src = p.mailbox[p.rank] + bank + lane;  // GPU `lane`'s slot in my mailbox
-    const unsigned long long flag = p.seq & 0xffffffffull;
+    const unsigned long long flag = seq & 0xffffffffull;
     const unsigned long long t0 = global_timer_ns();
     unsigned long long w0, w1 = flag << 32;
     for (;;) {
       w0 = ld_relaxed_sys(&src->w[0]);
       if constexpr (sizeof(T) == 8) w1 = ld_relaxed_sys(&src->w[1]);
       if ((w0 >> 32) == flag && (w1 >> 32) == flag) break;
-      if (global_timer_ns() - t0 > 2000000000ull) { ok = false; break; }
+      if (global_timer_ns() - t0 > p.timeout_ns) { ok = false; break; }
     }
     got = from_bits<T>((w0 & 0xffffffffull) | (w1 << 32));
   }
   T total = T(0);
   for (int r = 0; r < p.world; r++) total = add_rn(total, __shfl_sync(0xffffffffu, got, r));  // rank order
-  if (!__all_sync(0xffffffffu, ok)) total = from_bits<T>(~0ull);  // NaN: a peer never arrived
+  if (!__all_sync(0xffffffffu, ok)) {
+    // a peer never arrived: the sum becomes NaN AND the failure is reported out of band, so that the
+    // host can tell it from NaN data (b200_dot returns B200_ETIMEOUT)
+    total = from_bits<T>(~0ull);
+    if (lane == 0) {
+      if (p.status_dev) *p.status_dev = 1u;
+      if (p.status_host) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p.status_host), "r"(1u) : "memory");
+    }
+  }
   return total;
 }
 
@@ -489,23 +541,26 @@ __device__ __forceinline__ T p2p_collect_warp(const P2PArgs& p) {
 // the MODE 2/3 kernels are register-capped by their launch bound instead (the spills land in this
 // once-per-launch code).  `pp` points INTO the __grid_constant__ parameter block: nothing is copied.
 template <typename T, bool COLLECT>
-__device__ __noinline__ T p2p_allreduce_warp(const P2PArgs* pp, T mine) {
-  p2p_send_warp<T>(*pp, mine);
-  if constexpr (COLLECT) return p2p_collect_warp<T>(*pp);
+__device__ __noinline__ T p2p_allreduce_warp(const P2PArgs* pp, T mine, unsigned long long seq) {
+  p2p_send_warp<T>(*pp, mine, seq);
+  if constexpr (COLLECT) return p2p_collect_warp<T>(*pp, seq);
   else return mine;
 }
 
 struct DotArgs {
   const void* a;
   const void* b;
-  void* partials;        // T[gridDim.x]
-  unsigned int* ticket;  // zero before launch; left zero
+  void* partials;        // the workspace: T[gridDim.x] partials, then tickets and group sums (kDotWs* offsets)
   void* result_dev;      // may be null
   void* result_host;     // mapped pinned, may be null
   unsigned long long nvec, ntiles, n;
   unsigned int head;
   unsigned long long* bell_flag;  // doorbell (mapped pinned host word) rung after the result is stored, or nullptr
   unsigned long long bell_seq;
+  // Sequence numbers kept ON THE DEVICE (LEVEL 2): when non-null, the doorbell value is ++seq_counters[0] and the
+  // all-reduce sequence number ++seq_counters[1] instead of bell_seq / p2p.seq -- nothing in the parameter
+  // block changes from call to call, so the launch can be replayed from a CUDA graph.
+  unsigned long long* seq_counters;
   P2PArgs p2p;           // world <= 1: plain single-GPU dot
 };
 
@@ -529,7 +584,8 @@ __global__ void __launch_bounds__(dot_block_bound(VB, UNROLL, MODE), dot_min_blo
 dot_kernel(const __grid_constant__ DotArgs args) {
   constexpr int EPV = VB / (int)sizeof(T);
   __shared__ T scratch[32];
-  __shared__ bool is_last;
+  __shared__ bool group_last;
+  pdl_entry();
 
   const T* const a = static_cast<const T*>(args.a);
   const T* const b = static_cast<const T*>(args.b);
@@ -594,25 +650,48 @@ dot_kernel(const __grid_constant__ DotArgs args) {
   if (threadIdx.x == 0) partials[blockIdx.x] = sum;
 
   if constexpr (MODE != DOT_TWO_PASS) {
+    char* const ws = reinterpret_cast<char*>(args.partials);
+    unsigned int* const top_ticket = reinterpret_cast<unsigned int*>(ws + kDotWsTop);
+    T* const gsums = reinterpret_cast<T*>(ws + kDotWsGroupSums);
+    const unsigned ng = dot_num_groups(gridDim.x), g = blockIdx.x % ng;
+    unsigned int* const my_ticket = reinterpret_cast<unsigned int*>(ws + kDotWsGroupTickets) + g * kDotTicketStride;
+    const unsigned gsize = (gridDim.x - g + ng - 1) / ng;  // blocks in my group
     if (threadIdx.x == 0) {
       __threadfence();  // partial visible before the ticket is taken
-      const unsigned t = atomicAdd(args.ticket, 1u);
-      is_last = (t == gridDim.x - 1);
-      __threadfence();
+      group_last = atomicAdd(my_ticket, 1u) == gsize - 1;
     }
     __syncthreads();
-    if (is_last) {
-      T v = dot_second_pass<T>(partials, gridDim.x, scratch);
-      if (threadIdx.x == 0) *args.ticket = 0u;  // ready for the next launch
-      if constexpr (MODE >= DOT_TICKET_P2P) {   // fused all-reduce over peer memory (or its sending half)
-        if (threadIdx.x == 0) scratch[0] = v;
-        __syncthreads();
-        if (threadIdx.x < 32) v = p2p_allreduce_warp<T, MODE == DOT_TICKET_P2P>(&args.p2p, scratch[0]);
-      }
+    if (group_last && threadIdx.x < 32) {  // block-uniform; warp 0 of the last block of group g
+      __threadfence();  // acquire side: the group's partials
+      const T gs = dot_group_sum<T>(partials, gridDim.x, ng, g);
+      unsigned last = 0;
       if (threadIdx.x == 0) {
-        if (args.result_dev) *static_cast<T*>(args.result_dev) = v;
-        if (args.result_host) *static_cast<T*>(args.result_host) = v;
-        if (args.bell_flag) ring_host(args.bell_flag, args.bell_seq);  // release: after the result
+        gsums[g] = gs;
+        *my_ticket = 0u;  // ready for the next launch (stream order separates the launches)
+        __threadfence();
+        last = atomicAdd(top_ticket, 1u) == ng - 1;
+      }
+      last = __shfl_sync(0xffffffffu, last, 0);
+      if (last) {
+        __threadfence();
+        T v = dot_top_sum<T>(gsums, ng);
+        unsigned long long bell_seq = args.bell_seq, p2p_seq = args.p2p.seq;
+        if (threadIdx.x == 0) {
+          *top_ticket = 0u;
+          if (args.seq_counters) {  // this thread is the only one of the grid that touches the counters
+            bell_seq = args.seq_counters[0] + 1; args.seq_counters[0] = bell_seq;
+            if constexpr (MODE >= DOT_TICKET_P2P) { p2p_seq = args.seq_counters[1] + 1; args.seq_counters[1] = p2p_seq; }
+          }
+        }
+        if constexpr (MODE >= DOT_TICKET_P2P) {  // fused all-reduce over peer memory (or its sending half)
+          p2p_seq = __shfl_sync(0xffffffffu, p2p_seq, 0);
+          v = p2p_allreduce_warp<T, MODE == DOT_TICKET_P2P>(&args.p2p, __shfl_sync(0xffffffffu, v, 0), p2p_seq);
+        }
+        if (threadIdx.x == 0) {
+          if (args.result_dev) *static_cast<T*>(args.result_dev) = v;
+          if (args.result_host) *static_cast<T*>(args.result_host) = v;
+          if (args.bell_flag) ring_host(args.bell_flag, bell_seq);  // release: after the result
+        }
       }
     }
   }
@@ -623,7 +702,8 @@ template <typename T>
 __global__ void __launch_bounds__(32)
 dot_collect_kernel(const __grid_constant__ P2PArgs p, T* result_dev, T* result_host, unsigned long long* bell_flag,
                    unsigned long long bell_seq) {
-  const T v = p2p_collect_warp<T>(p);
+  pdl_entry();
+  const T v = p2p_collect_warp<T>(p, p.seq);
   if (threadIdx.x == 0) {
     if (result_dev) *result_dev = v;
     if (result_host) *result_host = v;
@@ -631,16 +711,28 @@ dot_collect_kernel(const __grid_constant__ P2PArgs p, T* result_dev, T* result_h
   }
 }
 
+// Second launch of the two-pass variant: warp g adds group g, then warp 0 adds the group sums -- the same
+// two functions, hence the same bits, as the ticket variant.
 template <typename T>
 __global__ void __launch_bounds__(1024)
 dot_final_kernel(const T* partials, unsigned nparts, T* result_dev, T* result_host, unsigned long long* bell_flag,
                  unsigned long long bell_seq) {
-  __shared__ T scratch[32];
-  const T v = dot_second_pass<T>(partials, nparts, scratch);
-  if (threadIdx.x == 0) {
-    if (result_dev) *result_dev = v;
-    if (result_host) *result_host = v;
-    if (bell_flag) ring_host(bell_flag, bell_seq);
+  __shared__ T gs[kDotGroups];
+  pdl_entry();
+  const unsigned ng = dot_num_groups(nparts), w = threadIdx.x >> 5;
+  if (w < ng) {
+    const T v = dot_group_sum<T>(partials, nparts, ng, w);
+    if ((threadIdx.x & 31u) == 0) gs[w] = v;
+  }
+  __syncthreads();
+  if (w == 0) {
+    const unsigned lane = threadIdx.x;
+    const T v = warp_sum(lane < ng ? gs[lane] : T(0));
+    if (lane == 0) {
+      if (result_dev) *result_dev = v;
+      if (result_host) *result_host = v;
+      if (bell_flag) ring_host(bell_flag, bell_seq);
+    }
   }
 }
 

@@ -40,10 +40,7 @@ int launch_ew_typed(const EwCall& call) {
   args.bell.ticket = static_cast<unsigned int*>(call.bell.ticket);
   args.bell.flag = static_cast<unsigned long long*>(call.bell.flag);
   args.bell.seq = call.bell.seq;
-  k<<<call.grid, call.r.block, 0, call.stream>>>(args, (T)call.s0, (T)call.s1, (T)call.s2);
-  count_launch();
-  B200_CUDA(cudaPeekAtLastError());
-  return B200_OK;
+  return launch_kernel(k, call.grid, call.r.block, 0, call.stream, call.r.flags, args, (T)call.s0, (T)call.s1, (T)call.s2);
 }
 
 template <int OP>

@@ -25,13 +25,10 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error_message() { return g_error; }
 
-// arrays a kernel touches (reads + writes, distinct arrays): decides whether the working set can
-// live in L2, in which case evict-first / no-allocate hints would destroy inter-kernel reuse.
-static int arrays_touched(int kernel) {
-  switch (kernel) {
-    case B200_COPY: case B200_MUL: case B200_DOT: return 2;
-    default: return 3;
-  }
+int size_class(size_t n, int elem_bytes, int l2_bytes) {
+  if (l2_bytes <= 0) l2_bytes = 126 << 20;
+  const double f = 3.0 * (double)n * elem_bytes / (double)l2_bytes;
+  return f <= 0.8 ? SIZE_L2 : f <= 3.2 ? SIZE_KNEE : f <= 8.0 ? SIZE_HBM : SIZE_HBM_XL;
 }
 
 int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
@@ -44,33 +41,46 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   if (num_sms <= 0) num_sms = 148;
   if (l2_bytes <= 0) l2_bytes = 126 << 20;
 
-  // BabelStream keeps all three arrays live across kernels, so L2 residency is judged on 3 arrays
-  const double footprint = 3.0 * (double)n * elem_bytes;
-  const bool l2_resident = footprint <= 0.8 * (double)l2_bytes;
-  const double bytes_moved = (double)arrays_touched(kernel) * (double)n * elem_bytes;
-  (void)bytes_moved;
+  // BabelStream keeps all three arrays live across kernels, so the size class is judged on 3 arrays
+  const int cls = size_class(n, elem_bytes, l2_bytes);
+  const bool l2_resident = cls == SIZE_L2;
 
   Resolved r;
   memset(&r, 0, sizeof r);
-  // ---- defaults (auto): winners of tools/sweep.py on B200, profiles/r01/sweep_f64.csv --------
-  // Elementwise kernels: one tile per block always beats a persistent grid-stride loop (by 4-10 %),
-  // and the best tile keeps ~32 bytes of loads in flight per thread at full occupancy -- the
-  // smallest in-flight window that still covers bandwidth x latency (Little's law), which keeps
-  // the DRAM pages touched concurrently few:
-  //     copy, mul      (1 load)   16-byte vectors x unroll 2, 512 threads   6.70 / 6.99 TB/s (2^25 / 2^29 fp64)
-  //     add, triad     (2 loads)  16-byte vectors x unroll 1, 512 threads   7.00 / 7.18-7.24
-  //     nstream        (3 loads)  16-byte vectors x unroll 2, 512 threads   7.16 / 7.33
-  //     init           (stores)   32-byte vectors x unroll 1, 256 threads   7.36 / 7.60
-  // Cache hints differ by < 0.5 %; evict_first wins narrowly beyond L2 and must be OFF for
-  // working sets that fit in L2, where it would destroy the reuse between consecutive kernels.
-  const int stream_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_EVICT_FIRST;
-  r.cache_hint = stream_hint;
   r.variant = B200_VARIANT_LDST;
-  r.grid_policy = INT_MAX;  // one tile per block
+  r.grid_policy = INT_MAX;  // one tile per block: always beats a persistent grid-stride loop (by 4-10 %)
+  // ---- the per-size table (auto) ------------------------------------------------------------------
+  // Sources: round 1 tools/sweep.py (profiles/r01/sweep_f64.csv: 6560 shapes, back to back) and round 2
+  // tools/lab/ew_lab (profiles/r02/lab_*.csv: blocking calls in the driver's kernel order, which is what
+  // src/main.cpp times).  Four classes by the footprint F of the three arrays against the L2 size:
+  //
+  //   SIZE_L2     F <= 0.8 L2   launch-latency bound (8-20 us per call): fat threads in small blocks, default
+  //                             cache policy so that consecutive kernels hit in L2
+  //   SIZE_KNEE   F <= 3.2 L2    part of every array still lives in L2 when the next kernel reads it: keep the
+  //                             lines (no evict-first), L1 no-allocate
+  //   SIZE_HBM    F <= 8 L2     HBM-bound, 50-250 us per call: ramp-up and tail are 3-4 % of the call, and they
+  //                             shrink with the tile -- 4 KB per array per block (256 threads x 16 B) runs the
+  //                             blocking call 2.3 us (triad, add) faster than 8 KB at 2^25 fp64 although both
+  //                             stream at the same 7.0 TB/s back to back
+  //   SIZE_HBM_XL beyond        steady state is everything: 8 KB per array per block streams 1.2-1.4 % faster at
+  //                             2^29 fp64 than 4 KB (7.21 vs 7.12 TB/s), the ~2 us of tail no longer matter
+  //
+  // All HBM classes: evict-first on loads AND stores.  Back to back the hints differ by < 0.5 %, but in the
+  // driver's sequence a kernel whose loads keep the default policy runs 3-4 us slower at 2^25 (its lines
+  // displace the previous kernel's dirty lines, whose write-back it then waits for).
+  // What did NOT help (profiles/r02/lab_notes.md): cp.async.bulk staging through shared memory with either
+  // register or bulk stores (the cub::DeviceTransform ublkcp shape), L2 prefetch ahead of the loads (per-line
+  // prefetch.global.L2 -- what the reference's thrust model runs -- or cp.async.bulk.prefetch.L2), persistent
+  // multi-stage rings: all within +-0.5 % of plain LDG/STG at 2^25 and 1-2.5 % slower at 2^29.
+  r.cache_hint = l2_resident ? B200_HINT_DEFAULT : cls == SIZE_KNEE ? B200_HINT_NOALLOC : B200_HINT_EVICT_FIRST;
   switch (kernel) {
     case B200_COPY: case B200_MUL: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
-    case B200_ADD: case B200_TRIAD: r.vec_bytes = 16; r.unroll = 1; r.block = 512; break;
-    case B200_NSTREAM: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
+    case B200_ADD: case B200_TRIAD:
+      r.vec_bytes = 16; r.unroll = 1; r.block = cls == SIZE_HBM_XL ? 512 : 256; break;
+    case B200_NSTREAM:
+      if (cls == SIZE_HBM_XL) { r.vec_bytes = 16; r.unroll = 2; r.block = 512; }
+      else { r.vec_bytes = 32; r.unroll = 1; r.block = 256; }
+      break;
     case B200_INIT: r.vec_bytes = 32; r.unroll = 1; r.block = 256; break;
     case B200_DOT:
       // read-only: a bounded grid-stride grid (the partials must fit the workspace).  Tuned in the
@@ -85,11 +95,10 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
       break;
   }
   if (l2_resident) {
-    // Working set inside L2 (<= 2^22 doubles): the call is launch-latency bound (8-20 us, of which
-    // ~9 us is launch + wait) and fatter threads in smaller blocks finish sooner; driver-timed
-    // candidates at 2^20..2^22, profiles/r01/small_size_candidates.txt.
+    // Working set inside L2 (<= 2^22 doubles): driver-timed candidates at 2^20..2^22,
+    // profiles/r01/small_size_candidates.txt and profiles/r02/lab_alt.txt
     if (kernel == B200_DOT) { r.vec_bytes = 32; r.unroll = 4; r.block = 256; r.grid_policy = -2; }
-    else { r.vec_bytes = 16; r.unroll = 4; r.block = 128; }
+    else { r.vec_bytes = 32; r.unroll = 1; r.block = 256; }
   }
   r.contract = 1;
   r.stages = 4;
@@ -105,6 +114,7 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   if (c.contract) r.contract = c.contract;
   if (c.stages) r.stages = c.stages;
   if (c.chunk_bytes) r.chunk_bytes = c.chunk_bytes;
+  r.flags = c.flags;
 
   // ---- validation ----
   if (r.vec_bytes != 8 && r.vec_bytes != 16 && r.vec_bytes != 32 && r.vec_bytes != elem_bytes) {
@@ -219,7 +229,7 @@ int b200_resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_b
     memset(out, 0, sizeof *out);
     out->vec_bytes = r.vec_bytes; out->unroll = r.unroll; out->block = r.block; out->grid = r.grid_policy;
     out->cache_hint = r.cache_hint; out->variant = r.variant; out->contract = r.contract;
-    out->stages = r.stages; out->chunk_bytes = r.chunk_bytes;
+    out->stages = r.stages; out->chunk_bytes = r.chunk_bytes; out->flags = r.flags;
   }
   if (grid_out) {
     // geometry for perfectly aligned arrays

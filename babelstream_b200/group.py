@@ -36,3 +36,11 @@ def connect_mailboxes(dist, rank: int, world: int):
 
 
 connect_mailboxes.last_error = ""
+
+
+def join_group(stream, dist, world: int, rank: int, mailbox) -> None:
+    """Make the single-GPU ``B200Stream`` rank ``rank`` of ``world`` and wait until every rank has done so.
+    ``b200_join_group`` wipes this rank's own mailbox and restarts its all-reduce sequence number; the barrier
+    guarantees that no peer's first partial can land before that wipe."""
+    stream.join_group(world, rank, mailbox.ptrs)
+    dist.barrier()

@@ -42,9 +42,13 @@ B200Stream<T>::B200Stream(BenchId bs, const intptr_t array_size, const int devic
   b200_device_info(device_id, &sms, &major, &minor, &mem, &l2, &clock_khz, &bus);
   std::cout << "B200 model: " << b200_version() << std::endl;
   std::cout << "CUDA Driver: " << getDeviceDriver(device_id) << std::endl;
+  // same fields as the reference's line (CUDAStream.cu:103-109): NVML's current memory clock, bus width, ECC
+  const int memclock = b200_device_mem_clock_mhz(device_id);
   std::cout << "CUDA Device " << device_id << ": \"" << name << "\" " << sms << " SMs(" << major << "," << minor << ") "
-            << "Memory: " << clock_khz / 1000 << " MHz x " << bus << "-bit = "
-            << 2.0 * (clock_khz / 1000.0) * (bus / 8) / 1000.0 << " GB/s PEAK, L2 " << (l2 >> 20) << " MiB" << std::endl;
+            << "Memory: " << memclock << " MHz x " << bus << "-bit = "
+            << 2.0 * memclock * (bus / 8) / 1000.0 << " GB/s PEAK, ECC is " << (b200_device_ecc(device_id) > 0 ? "ON" : "OFF")
+            << ", L2 " << (l2 >> 20) << " MiB" << std::endl;
+  std::cout << "Memory Allocation: " << b200_memory_mode(ctx) << std::endl;  // CUDAStream.cu:111-120
   char desc[4096] = "";
   if (b200_describe(ctx, desc, (int)sizeof desc) == B200_OK) std::cout << desc;
 

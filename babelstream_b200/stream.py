@@ -25,6 +25,8 @@ KERNELS = ["copy", "mul", "add", "triad", "dot", "nstream"]  # run order, src/be
 WEIGHTS = {"copy": 2, "mul": 2, "add": 3, "triad": 3, "dot": 2, "nstream": 4, "init": 3}
 HINTS = {"auto": 0, "default": 1, "noalloc": 2, "evict_first": 3, "stream": 4, "prefetch": 5}
 VARIANTS = {"auto": 0, "ldst": 1, "bulk": 2, "tma": 3, "two_pass": 1, "ticket": 2}
+LAUNCH_PDL = 1   # B200_LAUNCH_PDL: programmatic dependent launch (cfg.flags)
+ETIMEOUT = -7    # B200_ETIMEOUT
 
 START_A, START_B, START_C, START_SCALAR = 0.1, 0.2, 0.0, 0.4  # src/Stream.h:24-27
 
@@ -42,7 +44,7 @@ class LaunchCfg(C.Structure):
     """b200_launch_cfg.  All zero = auto."""
     _fields_ = [("vec_bytes", C.c_int), ("unroll", C.c_int), ("block", C.c_int), ("grid", C.c_int),
                 ("cache_hint", C.c_int), ("variant", C.c_int), ("contract", C.c_int), ("stages", C.c_int),
-                ("chunk_bytes", C.c_int), ("reserved", C.c_int * 3)]
+                ("chunk_bytes", C.c_int), ("flags", C.c_int), ("reserved", C.c_int * 2)]
 
     @classmethod
     def make(cls, **kw) -> "LaunchCfg":
@@ -107,7 +109,11 @@ def lib() -> C.CDLL:
         "b200_dot_mailbox_bytes": (sz, []),
         "b200_launch_dot_allreduce_p2p": (ci, [vp, vp, sz, ci, vp, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
         "b200_launch_dot_send_p2p": (ci, [vp, vp, sz, ci, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
-        "b200_launch_dot_collect_p2p": (ci, [ci, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), vp]),
+        "b200_launch_dot_collect_p2p": (ci, [ci, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), vp, ci, vp]),
+        "b200_dot_status_offset": (sz, []),
+        "b200_set_p2p_timeout_ms": (ci, [d]),
+        "b200_device_ecc": (ci, [ci]),
+        "b200_device_mem_clock_mhz": (ci, [ci]),
         "b200_launch_doorbell": (ci, [ci, vp, vp, vp, sz, ci, d, d, d, cfgp, C.POINTER(Doorbell), vp]),
         "b200_launch_dot_doorbell": (ci, [vp, vp, sz, ci, vp, vp, vp, cfgp, C.POINTER(Doorbell), vp]),
         "b200_dot_mailbox_create": (ci, [C.POINTER(vp)]),
@@ -133,6 +139,7 @@ def lib() -> C.CDLL:
         "b200_read_arrays": (ci, [vp, vp, vp, vp]),
         "b200_write_arrays": (ci, [vp, vp, vp, vp]),
         "b200_num_gpus": (ci, [vp]),
+        "b200_memory_mode": (cp, [vp]),
         "b200_array_size": (sz, [vp]),
         "b200_elem_bytes": (ci, [vp]),
         "b200_last_kernel_ms": (d, [vp]),
@@ -236,11 +243,20 @@ def launch_dot_send_p2p(a: int, b: int, n: int, elem_bytes: int, workspace: int,
 
 
 def launch_dot_collect_p2p(elem_bytes: int, result_dev: int, *, world: int, rank: int, seq: int, mailboxes,
-                           result_host_mapped: int = 0, stream: int = 0) -> None:
-    """LEVEL 1: one-warp kernel that waits for the partials of call `seq` and adds them in rank order."""
+                           result_host_mapped: int = 0, workspace: int = 0, flags: int = 0, stream: int = 0) -> None:
+    """LEVEL 1: one-warp kernel that waits for the partials of call `seq` and adds them in rank order.
+    `workspace` (optional): the dot workspace whose status word is set when a rank never arrives."""
     boxes = (C.c_void_p * len(mailboxes))(*mailboxes)
     _check(lib().b200_launch_dot_collect_p2p(elem_bytes, result_dev or None, result_host_mapped or None, world, rank, seq,
-                                             boxes, C.c_void_p(stream)))
+                                             boxes, workspace or None, flags, C.c_void_p(stream)))
+
+
+def dot_status_offset() -> int:
+    return int(lib().b200_dot_status_offset())
+
+
+def set_p2p_timeout_ms(ms: float) -> None:
+    _check(lib().b200_set_p2p_timeout_ms(float(ms)))
 
 
 def launch_doorbell(kernel: str, a: int, b: int, c: int, n: int, elem_bytes: int, bell: Doorbell, *,

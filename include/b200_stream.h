@@ -34,6 +34,7 @@ extern "C" {
 #define B200_ECUDA (-4)     /* a CUDA runtime call failed (reference: CU() macro, CUDAStream.cu:14-26) */
 #define B200_ENCCL (-5)     /* NCCL missing or failed (multi-GPU dot only) */
 #define B200_EUNSUPPORTED (-6)
+#define B200_ETIMEOUT (-7)  /* the peer-memory all-reduce gave up waiting for a rank (multi-GPU dot); the sum is NaN */
 
 /* Kernel ids: the reference's BenchId values (src/benchmark.h:18) plus init. */
 enum { B200_COPY = 0, B200_MUL = 1, B200_ADD = 2, B200_TRIAD = 3, B200_NSTREAM = 4, B200_DOT = 5, B200_INIT = 6,
@@ -71,8 +72,15 @@ typedef struct b200_launch_cfg {
                      2 unfused: round(s*c) then add, the reference built -ffp-contract=off */
   int stages;     /* bulk/tma copy: ring depth (0 auto) */
   int chunk_bytes;/* bulk/tma copy: bytes per stage (0 auto) */
-  int reserved[3];
+  int flags;      /* B200_LAUNCH_* bits (LEVEL 1 only) */
+  int reserved[2];
 } b200_launch_cfg;
+
+/* flags */
+#define B200_LAUNCH_PDL 1 /* programmatic dependent launch: the kernel may be SCHEDULED before the previous kernel of
+                             the stream has drained; it waits (griddepcontrol.wait) for that kernel's completion and
+                             memory before its first access, so stream-order semantics are unchanged.  Removes the
+                             ~2 us drain-and-launch gap between back-to-back kernels of an asynchronous sequence. */
 
 /* ------------------------------------------------------------------------------------------
  * LEVEL 0 -- library / device queries (replace listDevices / getDeviceName / getDeviceDriver,
@@ -85,6 +93,9 @@ int b200_device_name(int device, char* buf, int buflen);
 int b200_driver_version(int device);                   /* cudaDriverGetVersion value, or negative */
 int b200_device_info(int device, int* num_sms, int* cc_major, int* cc_minor, size_t* total_mem,
                      int* l2_bytes, int* mem_clock_khz, int* mem_bus_bits);
+int b200_device_ecc(int device);                       /* 1 = ECC on, 0 = off (banner: CUDAStream.cu:108-109) */
+int b200_device_mem_clock_mhz(int device);             /* NVML's current memory clock as the reference prints it
+                                                          (CUDAStream.cu:96-108); the attribute's value without NVML */
 uint64_t b200_launch_count(void);                      /* kernels launched by this library so far */
 
 /* Host-side logic, usable (and tested) without a GPU. */
@@ -99,7 +110,8 @@ int b200_resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_b
 /* ------------------------------------------------------------------------------------------
  * LEVEL 1 -- raw launchers: one kernel on caller-owned DEVICE pointers, asynchronous on
  * `stream` (a cudaStream_t passed as void*; NULL = the legacy default stream) of the CURRENT
- * device.  Any pointer alignment and any n >= 0 are accepted.
+ * device.  Any pointer alignment and any n >= 0 are accepted.  The array a kernel writes must not overlap the
+ * arrays it reads (they are loaded through the read-only path): in-place calls return B200_EINVAL.
  * Each replaces the body of the reference model's method of the same name:
  *   init_arrays CUDAStream.cu:203-211   copy :237-243   mul :245-251   add :253-259
  *   triad :261-267   nstream :269-275   dot :277-309
@@ -131,7 +143,7 @@ int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void
  * mailbox (b200_dot_mailbox_bytes() of zero-initialised device memory on GPU g, peer access enabled
  * from the current device); `seq` must be non-zero, equal on all GPUs and strictly increasing from
  * call to call.  All `world` launches must be issued (on their own devices) for any to complete;
- * a peer that never arrives turns the result into NaN after 2 s instead of hanging. */
+ * a peer that never arrives turns the result into NaN after the timeout below instead of hanging. */
 size_t b200_dot_mailbox_bytes(void);
 int b200_launch_dot_allreduce_p2p(const void* a, const void* b, size_t n, int elem_bytes, void* workspace,
                                   void* result_dev, void* result_host_mapped, int world, int rank,
@@ -149,7 +161,13 @@ int b200_launch_dot_send_p2p(const void* a, const void* b, size_t n, int elem_by
                              int world, int rank, unsigned long long seq, void* const* mailboxes,
                              const b200_launch_cfg* cfg, void* stream);
 int b200_launch_dot_collect_p2p(int elem_bytes, void* result_dev, void* result_host_mapped, int world, int rank,
-                                unsigned long long seq, void* const* mailboxes, void* stream);
+                                unsigned long long seq, void* const* mailboxes, void* workspace /* may be NULL */,
+                                int flags /* B200_LAUNCH_* */, void* stream);
+/* A rank that never sends turns the sum into NaN after the timeout (default 2000 ms, BABELSTREAM_B200_P2P_TIMEOUT_MS)
+ * AND sets the 32-bit word at byte b200_dot_status_offset() of the dot workspace to 1 (never cleared by a kernel), so
+ * that the failure can be told from NaN data; LEVEL 2's b200_dot returns B200_ETIMEOUT. */
+size_t b200_dot_status_offset(void);
+int b200_set_p2p_timeout_ms(double ms);
 
 /* Completion doorbell: lets a BLOCKING caller learn that a kernel has finished without
  * cudaStreamSynchronize.  Every block takes a ticket once its stores are fenced; the block that takes
@@ -248,6 +266,7 @@ int b200_write_arrays(b200_ctx* ctx, const void* a, const void* b, const void* c
 
 /* Introspection */
 int b200_num_gpus(b200_ctx* ctx);
+const char* b200_memory_mode(b200_ctx* ctx); /* "DEFAULT" | "MANAGED" | "PAGEFAULT": the reference's "Memory Allocation:" banner line */
 size_t b200_array_size(b200_ctx* ctx);
 int b200_elem_bytes(b200_ctx* ctx);
 /* Device time of the last kernel call in milliseconds, max over GPUs, measured with CUDA events

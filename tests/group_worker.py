@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 import babelstream_b200 as bs  # noqa: E402
-from babelstream_b200.group import connect_mailboxes  # noqa: E402
+from babelstream_b200.group import connect_mailboxes, join_group  # noqa: E402
 
 
 def main():
@@ -34,7 +34,7 @@ def main():
             want = dtype(0)
             for p in parts:                          # rank order, in type T: what the kernel does
                 want = dtype(want + np.frombuffer(p, dtype=dtype)[0])
-            s.join_group(world, rank, mb.ptrs)
+            join_group(s, dist, world, rank, mb)     # join + barrier: the join wipes this rank's own mailbox
             assert "IPC mailboxes" in s.describe()
             got = [s.dot() for _ in range(7)]        # odd count: both mailbox banks, several rounds
             for g in got:
@@ -52,6 +52,7 @@ def main():
                 allv = [None] * world
                 dist.all_gather_object(allv, v1.tobytes())
                 assert all(x == allv[0] for x in allv), "ranks disagree on the all-reduced dot"
+            dist.barrier()
             s.join_group(1, 0, [])
             # LEVEL 1, the split all-reduce: send in the dot kernel, collect later -- same bits as the fused call
             mb2 = connect_mailboxes(dist, rank, world)

@@ -95,7 +95,7 @@ def test_resolve_cfg_defaults_and_overrides():
                                                                       cache_hint="stream", variant="bulk", contract="off"))
     assert (o.vec_bytes, o.unroll, o.block, o.grid, o.cache_hint, o.variant, o.contract) == (16, 8, 128, -3, 4, 2, 2)
     assert grid == 3 * 148
-    _, grid = bs.resolve_cfg("add", 1000, 8, num_sms=148, cfg=bs.LaunchCfg.make(grid=-8, unroll=1, block=256))
+    _, grid = bs.resolve_cfg("add", 1000, 8, num_sms=148, cfg=bs.LaunchCfg.make(grid=-8, vec_bytes=16, unroll=1, block=256))
     assert grid == 2, "never more blocks than tiles (500 16-byte vectors / 256 threads = 2 tiles)"
     scalar, _ = bs.resolve_cfg("mul", 1000, 4, cfg=bs.LaunchCfg.make(vec_bytes=4))
     assert scalar.unroll == 4 and scalar.cache_hint == 1, "the float scalar path has one compiled shape"
@@ -108,6 +108,28 @@ def test_resolve_cfg_defaults_and_overrides():
 def test_resolve_cfg_rejects(bad):
     with pytest.raises(bs.B200Error):
         bs.resolve_cfg("triad", 1 << 20, 8, cfg=bs.LaunchCfg.make(**bad))
+
+
+def test_resolve_cfg_size_classes():
+    """The per-size table of csrc/tuning.cu: four classes by the footprint of the three arrays against L2."""
+    l2 = 126 << 20
+    shapes = {}
+    for log2n in range(18, 31):
+        t, _ = bs.resolve_cfg("triad", 1 << log2n, 8, num_sms=148, l2_bytes=l2)
+        shapes[log2n] = (t.vec_bytes, t.unroll, t.block, t.cache_hint)
+    assert shapes[20] == shapes[22] and shapes[20][3] == bs.HINTS["default"], "L2-resident: default cache policy"
+    assert shapes[23][3] == bs.HINTS["noalloc"] and shapes[24][3] == bs.HINTS["noalloc"], "knee: keep the lines in L2"
+    assert shapes[25][3] == bs.HINTS["evict_first"] and shapes[29][3] == bs.HINTS["evict_first"], "HBM-bound: evict-first"
+    tile = lambda s: s[0] * s[1] * s[2]
+    assert tile(shapes[25]) < tile(shapes[29]), "short HBM-bound calls run smaller tiles (ramp-up and tail) than 2^29"
+    # the class depends on BYTES, not elements: fp32 at 2n is the same class as fp64 at n
+    for log2n in range(19, 30):
+        d, _ = bs.resolve_cfg("add", 1 << log2n, 8, num_sms=148, l2_bytes=l2)
+        f, _ = bs.resolve_cfg("add", 1 << (log2n + 1), 4, num_sms=148, l2_bytes=l2)
+        assert (d.vec_bytes, d.unroll, d.block, d.cache_hint) == (f.vec_bytes, f.unroll, f.block, f.cache_hint)
+    # flags travel through the resolver untouched
+    o, _ = bs.resolve_cfg("triad", 1 << 25, 8, cfg=bs.LaunchCfg.make(flags=bs.LAUNCH_PDL))
+    assert o.flags == bs.LAUNCH_PDL
 
 
 def test_resolve_cfg_kernel_specific_rules():
@@ -159,8 +181,8 @@ def test_bench_reference_arm_prints_one_contract_line():
     same metric / unit / config keys as the b200 arm (the driver computes the ratio itself)."""
     import json
     import subprocess
-    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1"],
-                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1",
+                        "--no-extras"], capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert p.returncode == 0, p.stderr
     lines = [l for l in p.stdout.splitlines() if l.strip()]
     assert len(lines) == 1
@@ -172,10 +194,28 @@ def test_bench_reference_arm_prints_one_contract_line():
     assert d["config"]["elements_per_gpu"] == 1 << bench.LOG2N and d["config"]["kernels"] == bench.KERNEL_ORDER
     assert d["config"]["bytes_per_step_per_gpu"] == 16 * 8 * (1 << bench.LOG2N)
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["value"] == d["value"] > 0 and "omp-stream" in cb["sample"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["value"] == d["value"] > 0 and "OMPStream.cpp" in cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": bench.UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    # both arms print the SAME config (key for key) and the same warm-up count, so that the driver's
+    # same_config / same_steps checks hold
+    assert d["config"] == bench.make_config(bench.LOG2N, 1) and d["warmup"] == 3
     # value = algorithmic bytes of a step / time of a step
     assert abs(d["value"] - 16 * 8 * (1 << bench.LOG2N) / (d["ms_per_step"] * 1e-3) / 1e9) < 0.05 * d["value"]
+
+
+def test_bench_gold_recurrence_matches_the_oracle_bit_for_bit():
+    """bench.py's parity key computes check_solution's gold values itself (exact rational fma); it must agree with
+    the oracle's restatement of src/main.cpp:331-370 in both contraction modes."""
+    sys.path.insert(0, ROOT)
+    import bench
+    import oracle as O
+    orc = O.Oracle()
+    for steps in (1, 2, 3, 10, 100):
+        for contract in (True, False):
+            g = orc.gold(np.float64, O.ALL, O.ORDER_CLASSIC, steps, 1 << 20, contract=contract)
+            a, b, c, a_dot, b_dot = bench.gold_recurrence(steps, contract)
+            assert [float(x).hex() for x in g[:3]] == [a.hex(), b.hex(), c.hex()], (steps, contract)
+            assert (a_dot * b_dot * float(1 << 20)).hex() == float(g[3]).hex()
 
 
 def test_report_tool_renders_sweep_csv(tmp_path):

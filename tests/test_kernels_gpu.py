@@ -366,3 +366,49 @@ def test_doorbell_rings_after_the_results_are_complete(orc, dtype):
         bs.launch_doorbell("copy", da.data_ptr(), 0, db.data_ptr(), n, a0.itemsize, bs.Doorbell(ticket.data_ptr(), flag.data_ptr(), 0), stream=st)
     with pytest.raises(bs.B200Error):
         bs.launch_doorbell("copy", da.data_ptr(), 0, db.data_ptr(), 0, a0.itemsize, bs.Doorbell(ticket.data_ptr(), flag.data_ptr(), 9), stream=st)
+
+
+def test_in_place_calls_are_rejected():
+    """The written array must not overlap a read array (they are loaded through ld.global.nc): B200_EINVAL."""
+    n, eb = 4096, 8
+    t = torch.zeros(3 * n, dtype=torch.float64, device="cuda")
+    a, b, c = t[:n], t[n:2 * n], t[2 * n:]
+    st = torch.cuda.current_stream().cuda_stream
+    with pytest.raises(bs.B200Error):
+        bs.launch("triad", a.data_ptr(), a.data_ptr(), c.data_ptr(), n, eb, stream=st)      # a = a + s*c
+    with pytest.raises(bs.B200Error):
+        bs.launch("add", a.data_ptr(), b.data_ptr(), a.data_ptr(), n, eb, stream=st)        # a = a + b
+    with pytest.raises(bs.B200Error):
+        bs.launch("copy", a.data_ptr(), 0, a.data_ptr() + 64, n - 8, eb, stream=st)         # overlapping ranges
+    bs.launch("triad", a.data_ptr(), c.data_ptr(), c.data_ptr(), n, eb, stream=st)          # two READ arrays may alias
+    bs.launch("nstream", a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, stream=st)        # a is read+written by design
+    torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_programmatic_dependent_launch_sequence_bit_exact(orc, dtype):
+    """cfg.flags = B200_LAUNCH_PDL: consecutive kernels of a stream overlap their launch with the predecessor's tail
+    and wait in griddepcontrol.wait before the first access.  Each kernel of the driver's sequence reads what the
+    previous one wrote, so any early access would show up as wrong bits."""
+    tt = torch.float64 if dtype is np.float64 else torch.float32
+    eb = np.dtype(dtype).itemsize
+    u = np.uint64 if dtype is np.float64 else np.uint32
+    st = torch.cuda.current_stream().cuda_stream
+    for n in (1000, (1 << 22) + 5):
+        a = torch.empty(n, dtype=tt, device="cuda"); b = torch.empty_like(a); c = torch.empty_like(a)
+        ws = torch.zeros(bs.dot_workspace_bytes(), dtype=torch.uint8, device="cuda")
+        out = torch.zeros(1, dtype=tt, device="cuda")
+        cfg = bs.LaunchCfg.make(flags=bs.LAUNCH_PDL)
+        bs.launch("init", a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, cfg=cfg, stream=st)
+        steps = 6
+        for _ in range(steps):
+            for k in ("copy", "mul", "add", "triad"):
+                bs.launch(k, a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, cfg=cfg, stream=st)
+            bs.launch_dot(a.data_ptr(), b.data_ptr(), n, eb, ws.data_ptr(), out.data_ptr(), cfg=cfg, stream=st)
+            bs.launch("nstream", a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, cfg=cfg, stream=st)
+        torch.cuda.synchronize()
+        g = orc.gold(dtype, O.ALL, O.ORDER_CLASSIC, steps, n)
+        for arr, gold in ((a, g[0]), (b, g[1]), (c, g[2])):
+            assert (arr.cpu().numpy().view(u) == np.asarray(gold).view(u)).all(), n
+        eps = np.finfo(dtype).eps
+        assert abs(float(out.item()) - float(g[3])) <= 64 * eps * abs(float(g[3]))

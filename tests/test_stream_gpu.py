@@ -127,6 +127,7 @@ def test_options_and_variants(orc):
     ref = None
     for opts in ({}, {"copy_variant": "bulk"}, {"copy_variant": "tma"}, {"dot_variant": "two_pass"},
                  {"sync": "spin"}, {"sync": "stream"}, {"sync": "doorbell"}, {"sync": "doorbell", "dot_variant": "two_pass"},
+                 {"launch": "direct"}, {"launch": "direct", "sync": "doorbell"}, {"launch": "graph", "dot_variant": "two_pass"},
                  {"timing": "1"}, {"timing": "1", "sync": "doorbell"}, {"tune": "all:vec=16,unroll=4,hint=3,grid=-4;dot:vec=32,unroll=2,block=256"}):
         with bs.B200Stream(n, dtype=np.float64, **opts) as s:
             total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)
@@ -161,6 +162,83 @@ def test_wait_modes_bit_exact_at_every_size_class(orc, dtype):
                 ref = ref or cur
                 assert cur == ref, (n, sync)
 
+
+
+def test_plans_replay_and_follow_the_arguments(orc):
+    """Every LEVEL 2 call replays a captured one-kernel graph (launch=graph, the default).  The plan is keyed on the
+    scalar and on the options: changing either must rebuild it, and replays are counted as launches."""
+    n = (1 << 16) + 3
+    with bs.B200Stream(n, dtype=np.float64) as s, bs.B200Stream(n, dtype=np.float64, launch="direct") as d:
+        assert "CUDA graph" in s.describe() and "direct" in d.describe()
+        c0 = bs.launch_count()
+        for _ in range(5):
+            s.triad()
+        assert bs.launch_count() - c0 == 5, "one kernel per call, captured or replayed"
+        for scalar in (0.4, 0.25, -3.0, 0.4):
+            for x in (s, d):
+                x.init_arrays()
+                x.copy(); x.mul(scalar); x.add(); x.triad(scalar); x.nstream(scalar)
+            for ga, gd in zip(s.get_arrays(), d.get_arrays()):
+                assert np.array_equal(ga.view(np.uint64), gd.view(np.uint64)), scalar
+            assert s.dot().tobytes() == d.dot().tobytes()
+        # an option change between calls (new launch shape) is picked up by the next call
+        s.set_option("tune", "triad:vec=8,unroll=4,block=128,hint=1")
+        d.set_option("tune", "triad:vec=8,unroll=4,block=128,hint=1")
+        s.triad(); d.triad()
+        assert np.array_equal(s.get_arrays()[0].view(np.uint64), d.get_arrays()[0].view(np.uint64))
+        # many dots in a row: the doorbell value lives on the device and must stay in step with the host
+        want = d.dot().tobytes()
+        for _ in range(300):
+            assert s.dot().tobytes() == want
+
+
+def test_gpu_dot_matches_reference_omp_model_on_random_data(orc):
+    """north_star: "match the reference's serial and OpenMP models".  dot of the UNMODIFIED OMPStream.cpp
+    (oracle/_ref/libref_omp.so) on seeded random data, within the driver's own bound (src/main.cpp:384)."""
+    if not O.Reference.available("omp"):
+        pytest.skip("oracle/_ref/libref_omp.so not built")
+    for dtype in (np.float64, np.float32):
+        n = (1 << 20) + 11
+        rng = np.random.default_rng(2025)
+        a0 = rng.uniform(0.5, 1.5, n).astype(dtype)
+        b0 = rng.uniform(0.5, 1.5, n).astype(dtype)
+        c0 = rng.uniform(0.5, 1.5, n).astype(dtype)
+        ref = O.Reference("omp", dtype, n)
+        ref.set(a0, b0, c0)
+        want = float(ref.dot())
+        ref.close()
+        with bs.B200Stream(n, dtype=dtype) as s:
+            s.write_arrays(a0, b0, c0)
+            got = float(s.dot())
+        eps = np.finfo(dtype).eps
+        assert abs(got - want) <= 1e7 * eps * max(abs(got), abs(want)), (dtype, got, want)
+        # and far tighter than that against the exact sum: both are sums of n positive terms
+        exact = float(np.dot(a0.astype(np.float64), b0.astype(np.float64)))
+        assert abs(got - exact) <= 64 * eps * np.log2(n) * abs(exact), (dtype, got, exact)
+
+
+def test_dot_allreduce_timeout_is_an_error_not_a_nan(orc):
+    """A rank that never sends its partial: the fused all-reduce gives up after the configured bound,
+    and b200_dot reports B200_ETIMEOUT instead of handing back a NaN that looks like data.  One GPU is enough:
+    rank 1's mailbox is a second allocation on the same device and nobody ever writes to it."""
+    import ctypes as C
+    n = 4096
+    bs.set_p2p_timeout_ms(50.0)
+    try:
+        mine, silent = bs.Mailbox(), bs.Mailbox()
+        with bs.B200Stream(n, dtype=np.float64) as s:
+            alone = s.dot()
+            s.join_group(2, 0, [mine.ptr, silent.ptr])
+            with pytest.raises(bs.B200Error) as e:
+                s.dot()
+            assert e.value.code == bs.ETIMEOUT and "timed out" in str(e.value)
+            with pytest.raises(bs.B200Error):   # and again: the status word was cleared, the next call times out afresh
+                s.dot()
+            s.join_group(1, 0, [])
+            assert s.dot().tobytes() == alone.tobytes(), "leaving the group restores the single-GPU dot"
+        mine.close(); silent.close()
+    finally:
+        bs.set_p2p_timeout_ms(2000.0)
 
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 def test_managed_memory_mode(orc, dtype):
@@ -244,18 +322,28 @@ def test_constructor_errors():
 needs_bin = pytest.mark.skipif(not os.path.exists(BIN), reason="build/b200-stream not built (needs the reference tree)")
 
 
-def run_bin(*args, env=None):
+CMAKE_BIN = os.path.join(ROOT, "build", "cmake", "b200-stream")
+
+
+def run_bin(*args, env=None, exe=BIN):
     e = dict(os.environ)
     e.update(env or {})
-    return subprocess.run([BIN, *args], capture_output=True, text=True, timeout=600, env=e)
+    return subprocess.run([exe, *args], capture_output=True, text=True, timeout=600, env=e)
 
 
-@needs_bin
-def test_driver_ci_sanity_case():
-    """The one run-time check of the reference's CI (src/ci-test-compile.sh:143-147), on our model."""
-    p = run_bin("-s", "1048576", "-n", "10")
+@pytest.mark.parametrize("exe", [BIN, CMAKE_BIN], ids=["makefile", "cmake-overlay"])
+def test_driver_ci_sanity_case(exe):
+    """The one run-time check of the reference's CI (src/ci-test-compile.sh:143-147), on our model -- for the
+    Makefile binary and for the one registered through the reference's cmake/register_models.cmake."""
+    if not os.path.exists(exe):
+        pytest.skip(f"{os.path.relpath(exe, ROOT)} not built (needs the reference tree" + (" and cmake)" if exe == CMAKE_BIN else ")"))
+    p = run_bin("-s", "1048576", "-n", "10", exe=exe)
     assert p.returncode == 0, p.stdout + p.stderr
     assert "Implementation: B200" in p.stdout and "Triad" in p.stdout and "FAILED" not in p.stderr
+    # the banner lines of the reference's model (src/cuda/CUDAStream.cu:103-121)
+    assert "ECC is O" in p.stdout and "Memory Allocation: DEFAULT" in p.stdout, p.stdout
+    q = run_bin("-s", "1048576", "-n", "10", "--only", "All", "--float", exe=exe)
+    assert q.returncode == 0, q.stdout + q.stderr
 
 
 @needs_bin
@@ -276,7 +364,7 @@ def test_driver_cli_matrix(args):
 def test_driver_managed_memory():
     p = run_bin("-s", str((1 << 22) + 3), "-n", "10", "--only", "All", env={"BABELSTREAM_B200_MEM": "managed"})
     assert p.returncode == 0, p.stdout + p.stderr
-    assert "MANAGED" in p.stdout
+    assert "Memory Allocation: MANAGED" in p.stdout
 
 
 @needs_bin

@@ -1,0 +1,861 @@
+// ew_lab.cu -- experimental bench for the elementwise kernels (round 2).  NOT part of the product:
+// a standalone program that times structurally different candidates for copy/mul/add/triad/nstream
+// before the winners are moved into babelstream_b200/csrc.  Build: make lab.  Run on the GPU box.
+//
+//   ew_lab b2b <log2n> <op> <level>      back-to-back launches, CUDA events (kernel steady state)
+//   ew_lab seq <log2n> <op> <level>      the driver's situation: the previous kernel of the sequence runs
+//                                        (untimed), then ONE blocking call of the candidate is timed with
+//                                        the host clock; min over iterations (src/main.cpp:154-165,319)
+//   ew_lab lat                           launch+wait latency of an empty kernel per stream / wait flavour
+//   ew_lab alt <log2n>                   per-kernel blocking minima of the whole sequence at an L2-resident
+//                                        size, our shape vs the reference's shape (the alternation puzzle)
+//
+// Candidates:
+//   ldg     vector LDG/STG, one tile per block or persistent; separate load/store cache hints; optional
+//           L2 prefetch of the tile `pfdist` tiles ahead (per-thread prefetch.global.L2 lines, what
+//           cub::DeviceTransform's prefetch algorithm does, or ONE cp.async.bulk.prefetch.L2 per array)
+//   staged  cp.async.bulk global->shared per tile (mbarrier), LDS.128, then STG.128 or a
+//           cp.async.bulk shared->global store; 1..S stages, one tile per block or persistent ring
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#define CK(x)                                                                                  \
+  do {                                                                                         \
+    cudaError_t e_ = (x);                                                                      \
+    if (e_ != cudaSuccess) {                                                                   \
+      std::fprintf(stderr, "CUDA error %s at %s:%d: %s\n", cudaGetErrorString(e_), __FILE__, __LINE__, #x); \
+      std::exit(2);                                                                            \
+    }                                                                                          \
+  } while (0)
+
+enum { OP_COPY = 0, OP_MUL = 1, OP_ADD = 2, OP_TRIAD = 3, OP_NSTREAM = 4 };
+static const char* kOpName[] = {"copy", "mul", "add", "triad", "nstream"};
+static const int kWeight[] = {2, 2, 3, 3, 4};
+
+// ---------------------------------------------------------------------------------------------------
+// hinted accesses
+// ---------------------------------------------------------------------------------------------------
+template <int VB> struct W;
+template <> struct W<8> { unsigned long long w[1]; };
+template <> struct W<16> { unsigned long long w[2]; };
+template <> struct W<32> { unsigned long long w[4]; };
+
+// load hints: 0 default   1 .L1::no_allocate   2 .L1::no_allocate + L2 evict_first;   NC adds .nc (read-only arrays)
+template <int VB, int H, bool NC>
+__device__ __forceinline__ W<VB> ld(const void* p, unsigned long long pol) {
+  W<VB> r;
+#define LDQ(Q)                                                                                                         \
+  if constexpr (VB == 8) asm volatile("ld.global" Q ".b64 %0, [%1];" : "=l"(r.w[0]) : "l"(p));                         \
+  else if constexpr (VB == 16) asm volatile("ld.global" Q ".v2.b64 {%0,%1}, [%2];" : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(p)); \
+  else asm volatile("ld.global" Q ".v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2]), "=l"(r.w[3]) : "l"(p));
+#define LDP(Q)                                                                                                         \
+  if constexpr (VB == 16)                                                                                              \
+    asm volatile("ld.global" Q ".L2::cache_hint.v2.b64 {%0,%1}, [%2], %3;" : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(p), "l"(pol)); \
+  else                                                                                                                 \
+    asm volatile("ld.global" Q ".L2::cache_hint.b64 %0, [%1], %2;" : "=l"(r.w[0]) : "l"(p), "l"(pol));
+  if constexpr (H == 0) { if constexpr (NC) { LDQ(".nc") } else { LDQ("") } }
+  else if constexpr (H == 1) { if constexpr (NC) { LDQ(".nc.L1::no_allocate") } else { LDQ(".L1::no_allocate") } }
+  else if constexpr (VB == 32) { if constexpr (NC) { LDQ(".nc.L1::no_allocate.L2::evict_first") } else { LDQ(".L1::no_allocate.L2::evict_first") } }
+  else { if constexpr (NC) { LDP(".nc.L1::no_allocate") } else { LDP(".L1::no_allocate") } }
+#undef LDQ
+#undef LDP
+  return r;
+}
+// store hints: 0 default   1 .L1::no_allocate   2 + L2 evict_first   3 .cs
+template <int VB, int H>
+__device__ __forceinline__ void st(void* p, const W<VB>& r, unsigned long long pol) {
+#define STQ(Q)                                                                                                         \
+  if constexpr (VB == 8) asm volatile("st.global" Q ".b64 [%0], %1;" ::"l"(p), "l"(r.w[0]) : "memory");                \
+  else if constexpr (VB == 16) asm volatile("st.global" Q ".v2.b64 [%0], {%1,%2};" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]) : "memory"); \
+  else asm volatile("st.global" Q ".v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]), "l"(r.w[2]), "l"(r.w[3]) : "memory");
+  if constexpr (H == 0) { STQ("") }
+  else if constexpr (H == 1) { STQ(".L1::no_allocate") }
+  else if constexpr (H == 3) { STQ(".cs") }
+  else if constexpr (VB == 32) { STQ(".L1::no_allocate.L2::evict_first") }
+  else if constexpr (VB == 16)
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v2.b64 [%0], {%1,%2}, %3;" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]), "l"(pol) : "memory");
+  else
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.b64 [%0], %1, %2;" ::"l"(p), "l"(r.w[0]), "l"(pol) : "memory");
+#undef STQ
+}
+__device__ __forceinline__ unsigned long long evict_first_policy() {
+  unsigned long long p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+
+template <int OP>
+__device__ __forceinline__ double apply(double a, double b, double c, double s) {
+  if constexpr (OP == OP_COPY) return a;
+  else if constexpr (OP == OP_MUL) return __dmul_rn(s, c);
+  else if constexpr (OP == OP_ADD) return __dadd_rn(a, b);
+  else if constexpr (OP == OP_TRIAD) return __fma_rn(s, c, b);
+  else return __dadd_rn(a, __fma_rn(s, c, b));
+}
+template <int OP> struct Uses {
+  static constexpr bool A = OP == OP_COPY || OP == OP_ADD || OP == OP_NSTREAM;
+  static constexpr bool B = OP == OP_ADD || OP == OP_TRIAD || OP == OP_NSTREAM;
+  static constexpr bool C = OP == OP_MUL || OP == OP_TRIAD || OP == OP_NSTREAM;
+  static constexpr int NIN = (A ? 1 : 0) + (B ? 1 : 0) + (C ? 1 : 0);
+  // output array: copy, add -> c   mul -> b   triad, nstream -> a
+  static constexpr int OUT = (OP == OP_COPY || OP == OP_ADD) ? 2 : OP == OP_MUL ? 1 : 0;
+};
+
+struct Arrays { double *a, *b, *c; };
+__device__ __forceinline__ char* arr(const Arrays& x, int i) { return reinterpret_cast<char*>(i == 0 ? x.a : i == 1 ? x.b : x.c); }
+
+// ---------------------------------------------------------------------------------------------------
+// ldg kernel
+// ---------------------------------------------------------------------------------------------------
+// programmatic dependent launch: let the NEXT kernel of the stream be scheduled as soon as every block of this
+// one has started, and wait for the PREVIOUS kernel's memory before touching anything (both are no-ops when
+// the launch carries no programmatic dependency)
+__device__ __forceinline__ void pdl_entry() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+struct LdgArgs {
+  Arrays x;
+  unsigned long long nvec, ntiles;
+  double s;
+  int pf;                  // 0 none, 1 per-thread prefetch.global.L2 of the lines, 2 bulk prefetch by one thread
+  unsigned long long pfdist;  // tiles ahead (0 = the tile about to be loaded)
+};
+
+__device__ __forceinline__ void prefetch_line(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p) : "memory"); }
+__device__ __forceinline__ void prefetch_bulk(const void* p, unsigned bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
+template <int OP, int VB, int UNROLL, int LDH, int STH>
+__global__ void __launch_bounds__(VB * UNROLL <= 32 ? 1024 : 512)
+ldg_kernel(const LdgArgs g) {
+  using U = Uses<OP>;
+  pdl_entry();
+  constexpr int EPV = VB / 8;
+  const unsigned long long pol = (LDH == 2 || STH == 2) ? evict_first_policy() : 0ull;
+  const unsigned long long tile_vecs = (unsigned long long)blockDim.x * UNROLL;
+  char* const pa = arr(g.x, 0); char* const pb = arr(g.x, 1); char* const pc = arr(g.x, 2);
+  char* const po = arr(g.x, U::OUT);
+  for (unsigned long long tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x) {
+    if (g.pf) {
+      const unsigned long long pt = tile + g.pfdist;
+      if (pt < g.ntiles) {
+        const unsigned long long off = pt * tile_vecs * VB;
+        const unsigned bytes = (unsigned)(tile_vecs * VB);
+        if (g.pf == 1) {
+          for (unsigned o = threadIdx.x * 128u; o < bytes; o += blockDim.x * 128u) {
+            if (U::A) prefetch_line(pa + off + o);
+            if (U::B) prefetch_line(pb + off + o);
+            if (U::C) prefetch_line(pc + off + o);
+          }
+        } else if (threadIdx.x == 0) {
+          if (U::A) prefetch_bulk(pa + off, bytes);
+          if (U::B) prefetch_bulk(pb + off, bytes);
+          if (U::C) prefetch_bulk(pc + off, bytes);
+        }
+      }
+    }
+    const unsigned long long v0 = tile * tile_vecs + threadIdx.x;
+    W<VB> wa[UNROLL], wb[UNROLL], wc[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; j++) {
+      const unsigned long long v = v0 + (unsigned long long)j * blockDim.x;
+      if (v < g.nvec) {
+        if constexpr (U::A) wa[j] = ld<VB, LDH, OP != OP_NSTREAM>(pa + v * VB, pol);
+        if constexpr (U::B) wb[j] = ld<VB, LDH, true>(pb + v * VB, pol);
+        if constexpr (U::C) wc[j] = ld<VB, LDH, true>(pc + v * VB, pol);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; j++) {
+      const unsigned long long v = v0 + (unsigned long long)j * blockDim.x;
+      if (v < g.nvec) {
+        W<VB> r;
+#pragma unroll
+        for (int e = 0; e < EPV; e++) {
+          const double a = U::A ? __longlong_as_double((long long)wa[j].w[e]) : 0.0;
+          const double b = U::B ? __longlong_as_double((long long)wb[j].w[e]) : 0.0;
+          const double c = U::C ? __longlong_as_double((long long)wc[j].w[e]) : 0.0;
+          r.w[e] = (unsigned long long)__double_as_longlong(apply<OP>(a, b, c, g.s));
+        }
+        st<VB, STH>(po + v * VB, r, pol);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// staged kernel
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nLAB_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra LAB_DONE_%=;\nbra LAB_WAIT_%=;\nLAB_DONE_%=:\n}" ::"r"(s32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* sdst, const void* gsrc, unsigned bytes, uint64_t* bar, unsigned long long pol) {
+  if (pol)
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(s32(sdst)), "l"(gsrc), "r"(bytes), "r"(s32(bar)), "l"(pol) : "memory");
+  else
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s32(sdst)), "l"(gsrc), "r"(bytes), "r"(s32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, unsigned bytes, unsigned long long pol) {
+  if (pol)
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst), "r"(s32(ssrc)), "r"(bytes), "l"(pol) : "memory");
+  else
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(s32(ssrc)), "r"(bytes) : "memory");
+}
+
+struct StagedArgs {
+  Arrays x;
+  unsigned long long ntiles;
+  unsigned tile_bytes;  // per array, multiple of 16
+  int stages;
+  int ld_evict_first, st_evict_first;
+  double s;
+};
+constexpr int kMaxStages = 8;
+
+template <int OP, bool BULK_STORE, int STH>
+__global__ void __launch_bounds__(1024)
+staged_kernel(const StagedArgs g) {
+  using U = Uses<OP>;
+  extern __shared__ __align__(128) char smem[];
+  __shared__ uint64_t full[kMaxStages];
+  const int S = g.stages;
+  const unsigned tb = g.tile_bytes;
+  const unsigned stage_bytes = tb * U::NIN;
+  const unsigned long long first = blockIdx.x, stride = gridDim.x;
+  if (first >= g.ntiles) return;
+  const unsigned long long mine = (g.ntiles - first + stride - 1) / stride;
+  const unsigned long long pol = (g.ld_evict_first || g.st_evict_first) ? evict_first_policy() : 0ull;
+  const unsigned long long ldpol = g.ld_evict_first ? pol : 0ull, stpol = g.st_evict_first ? pol : 0ull;
+  char* const po = arr(g.x, U::OUT);
+
+  auto issue = [&](unsigned long long k) {
+    const int s = (int)(k % S);
+    const unsigned long long off = (first + k * stride) * tb;
+    char* dst = smem + (size_t)s * stage_bytes;
+    mbar_expect_tx(&full[s], stage_bytes);
+    if (U::A) { bulk_load(dst, arr(g.x, 0) + off, tb, &full[s], ldpol); dst += tb; }
+    if (U::B) { bulk_load(dst, arr(g.x, 1) + off, tb, &full[s], ldpol); dst += tb; }
+    if (U::C) { bulk_load(dst, arr(g.x, 2) + off, tb, &full[s], ldpol); }
+  };
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; s++) mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    const unsigned long long pre = mine < (unsigned long long)S ? mine : (unsigned long long)S;
+    for (unsigned long long k = 0; k < pre; k++) issue(k);
+  }
+  __syncthreads();
+  const unsigned nv = tb / 16;
+  for (unsigned long long k = 0; k < mine; k++) {
+    const int s = (int)(k % S);
+    mbar_wait(&full[s], (unsigned)((k / S) & 1));
+    char* const sb = smem + (size_t)s * stage_bytes;
+    const double2* sa2 = reinterpret_cast<const double2*>(sb);
+    const double2* sb2 = reinterpret_cast<const double2*>(sb + (U::A ? tb : 0));
+    const double2* sc2 = reinterpret_cast<const double2*>(sb + ((U::A ? tb : 0) + (U::B ? tb : 0)));
+    char* const gout = po + (first + k * stride) * tb;
+#pragma unroll 4
+    for (unsigned v = threadIdx.x; v < nv; v += blockDim.x) {
+      double2 a = make_double2(0, 0), b = a, c = a, r;
+      if constexpr (U::A) a = sa2[v];
+      if constexpr (U::B) b = sb2[v];
+      if constexpr (U::C) c = sc2[v];
+      r.x = apply<OP>(a.x, b.x, c.x, g.s);
+      r.y = apply<OP>(a.y, b.y, c.y, g.s);
+      if constexpr (BULK_STORE) {
+        reinterpret_cast<double2*>(sb)[v] = r;  // in place: slot v of the stage's first buffer is read by this thread only
+      } else {
+        W<16> w; w.w[0] = (unsigned long long)__double_as_longlong(r.x); w.w[1] = (unsigned long long)__double_as_longlong(r.y);
+        st<16, STH>(gout + (size_t)v * 16, w, stpol);
+      }
+    }
+    if constexpr (BULK_STORE) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if constexpr (BULK_STORE) {
+        bulk_store(gout, sb, tb, stpol);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        // refill the stage of the PREVIOUS store once that store has finished reading shared memory
+        if (k >= 1 && (k - 1) + S < mine) {
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          issue((k - 1) + S);
+        }
+      } else if (k + S < mine) {
+        issue(k + S);
+      }
+    }
+  }
+  if constexpr (BULK_STORE) {
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// helpers: init, check, dot stand-in (read a and b), empty
+// ---------------------------------------------------------------------------------------------------
+__global__ void fill_kernel(double* p, size_t n, double v) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+__global__ void check_kernel(const double* p, size_t n, double want, unsigned long long* bad) {
+  unsigned long long local = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    if (__double_as_longlong(p[i]) != __double_as_longlong(want)) local++;
+  if (local) atomicAdd(bad, local);
+}
+__global__ void readsum_kernel(const double* a, const double* b, size_t n, double* out) {
+  pdl_entry();
+  double acc = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) acc += a[i] * b[i];
+  if (acc == 1.2345e300) *out = acc;
+}
+__global__ void empty_kernel() {}
+// completion flag: bumps a device counter and stores it to a word of mapped pinned host memory
+__global__ void flag_kernel(unsigned long long* ctr, unsigned long long* host_flag) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const unsigned long long v = *ctr + 1;
+  *ctr = v;
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(host_flag), "l"(v) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------
+// configs
+// ---------------------------------------------------------------------------------------------------
+struct Cfg {
+  int kind = 0;  // 0 ldg, 1 staged
+  int op = OP_TRIAD;
+  int vb = 16, unroll = 1, ldh = 2, sth = 2, block = 512;
+  int grid = 0;  // 0: one tile per block; k > 0: k blocks per SM (persistent)
+  int pf = 0; long long pfdist = 0;
+  int tile = 8192, stages = 1, bulk_store = 0, ld_ef = 0, st_ef = 0;
+  std::string str() const {
+    char buf[256];
+    if (kind == 0)
+      std::snprintf(buf, sizeof buf, "ldg,vb=%d,u=%d,ldh=%d,sth=%d,block=%d,grid=%d,pf=%d,pfdist=%lld", vb, unroll, ldh, sth, block, grid, pf, pfdist);
+    else
+      std::snprintf(buf, sizeof buf, "staged,tile=%d,stages=%d,block=%d,grid=%d,bulkst=%d,sth=%d,ld_ef=%d,st_ef=%d", tile, stages, block, grid, bulk_store, sth, ld_ef, st_ef);
+    return buf;
+  }
+};
+
+static int g_sms = 148;
+static cudaStream_t g_stream;
+
+typedef void (*LdgFn)(const LdgArgs);
+typedef void (*StagedFn)(const StagedArgs);
+
+template <int OP, int VB, int UNROLL>
+static LdgFn pick_ldg_h(int ldh, int sth) {
+#define H(L, S) if (ldh == L && sth == S) return ldg_kernel<OP, VB, UNROLL, L, S>;
+  H(0, 0) H(0, 1) H(0, 2) H(0, 3) H(1, 0) H(1, 1) H(1, 2) H(1, 3) H(2, 0) H(2, 1) H(2, 2) H(2, 3)
+#undef H
+  return nullptr;
+}
+template <int OP>
+static LdgFn pick_ldg(const Cfg& c) {
+#define V(VB_, U_) if (c.vb == VB_ && c.unroll == U_) return pick_ldg_h<OP, VB_, U_>(c.ldh, c.sth);
+  V(8, 1) V(8, 2) V(8, 4) V(16, 1) V(16, 2) V(16, 4) V(32, 1) V(32, 2)
+#undef V
+  return nullptr;
+}
+template <int OP>
+static StagedFn pick_staged(const Cfg& c) {
+  if (c.bulk_store) return staged_kernel<OP, true, 0>;
+  switch (c.sth) {
+    case 0: return staged_kernel<OP, false, 0>;
+    case 1: return staged_kernel<OP, false, 1>;
+    case 2: return staged_kernel<OP, false, 2>;
+    case 3: return staged_kernel<OP, false, 3>;
+  }
+  return nullptr;
+}
+
+struct Launch {
+  bool ok = false;
+  LdgFn lf = nullptr; StagedFn sf = nullptr;
+  LdgArgs la; StagedArgs sa;
+  unsigned grid = 1, block = 128, smem = 0;
+  void go(cudaStream_t st = g_stream) const {
+    if (lf) lf<<<grid, block, 0, st>>>(la);
+    else sf<<<grid, block, smem, st>>>(sa);
+  }
+  // launched with the programmatic-stream-serialization attribute: may be scheduled before the previous
+  // kernel of the stream has drained (the kernel waits in griddepcontrol.wait)
+  void go_pdl(cudaStream_t st = g_stream) const {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = lf ? 0 : smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    if (lf) cudaLaunchKernelEx(&cfg, lf, la);
+    else cudaLaunchKernelEx(&cfg, sf, sa);
+  }
+};
+
+static Launch plan(const Cfg& c, Arrays x, size_t n, double s) {
+  Launch L;
+  L.block = c.block;
+  if (c.kind == 0) {
+    switch (c.op) {
+      case OP_COPY: L.lf = pick_ldg<OP_COPY>(c); break;
+      case OP_MUL: L.lf = pick_ldg<OP_MUL>(c); break;
+      case OP_ADD: L.lf = pick_ldg<OP_ADD>(c); break;
+      case OP_TRIAD: L.lf = pick_ldg<OP_TRIAD>(c); break;
+      default: L.lf = pick_ldg<OP_NSTREAM>(c); break;
+    }
+    if (!L.lf) return L;
+    if (c.block > (c.vb * c.unroll <= 32 ? 1024 : 512)) return L;
+    L.la.x = x; L.la.s = s; L.la.pf = c.pf; L.la.pfdist = (unsigned long long)c.pfdist;
+    L.la.nvec = n * 8 / c.vb;
+    const unsigned long long tv = (unsigned long long)c.block * c.unroll;
+    L.la.ntiles = (L.la.nvec + tv - 1) / tv;
+    L.grid = (unsigned)(c.grid > 0 ? std::min<unsigned long long>((unsigned long long)c.grid * g_sms, L.la.ntiles) : L.la.ntiles);
+  } else {
+    switch (c.op) {
+      case OP_COPY: L.sf = pick_staged<OP_COPY>(c); break;
+      case OP_MUL: L.sf = pick_staged<OP_MUL>(c); break;
+      case OP_ADD: L.sf = pick_staged<OP_ADD>(c); break;
+      case OP_TRIAD: L.sf = pick_staged<OP_TRIAD>(c); break;
+      default: L.sf = pick_staged<OP_NSTREAM>(c); break;
+    }
+    if (!L.sf) return L;
+    const int nin = c.op == OP_COPY || c.op == OP_MUL ? 1 : c.op == OP_NSTREAM ? 3 : 2;
+    if ((n * 8) % (size_t)c.tile) return L;
+    L.smem = (unsigned)(c.stages * nin * c.tile);
+    if (L.smem > 220 * 1024 || c.stages > kMaxStages) return L;
+    if (L.smem > 48 * 1024 && cudaFuncSetAttribute((const void*)L.sf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return L;
+    }
+    L.sa.x = x; L.sa.s = s; L.sa.tile_bytes = (unsigned)c.tile; L.sa.stages = c.stages;
+    L.sa.ld_evict_first = c.ld_ef; L.sa.st_evict_first = c.st_ef;
+    L.sa.ntiles = n * 8 / (size_t)c.tile;
+    if (c.grid == 0 && c.stages != 1) return L;  // one tile per block: a ring is pointless
+    L.grid = (unsigned)(c.grid > 0 ? std::min<unsigned long long>((unsigned long long)c.grid * g_sms, L.sa.ntiles) : L.sa.ntiles);
+  }
+  L.ok = true;
+  return L;
+}
+
+// the library's round-1 winners (tuning.cu), the baseline every candidate is compared with
+static Cfg baseline(int op) {
+  Cfg c; c.kind = 0; c.op = op; c.vb = 16; c.block = 512; c.ldh = 2; c.sth = 2; c.grid = 0;
+  c.unroll = (op == OP_ADD || op == OP_TRIAD) ? 1 : 2;
+  return c;
+}
+// the shape cub::DeviceTransform's prefetch algorithm runs for the reference's thrust model on sm_100
+static Cfg thrust_like(int op) {
+  Cfg c; c.kind = 0; c.op = op; c.vb = 8; c.block = 128; c.ldh = 0; c.sth = 0; c.grid = 0; c.pf = 1; c.pfdist = 0;
+  const int loaded = (op == OP_COPY || op == OP_MUL) ? 8 : op == OP_NSTREAM ? 24 : 16;
+  c.unroll = (49152 + 16 * 128 * loaded - 1) / (16 * 128 * loaded);  // ceil(min_bif / (occupancy * block * bytes))
+  if (c.unroll == 3) c.unroll = 4;
+  return c;
+}
+
+static std::vector<Cfg> candidates(int op, int level) {
+  std::vector<Cfg> v;
+  v.push_back(baseline(op));
+  v.push_back(thrust_like(op));
+  // 1. ldg: load/store hints separately, a few shapes
+  const int shapes[][3] = {{16, 1, 512}, {16, 2, 512}, {16, 1, 256}, {16, 2, 256}, {32, 1, 256}, {32, 1, 512}, {16, 4, 128}, {8, 2, 128}, {8, 4, 128}, {16, 1, 128}, {16, 2, 128}, {16, 1, 1024}};
+  for (auto& sh : shapes) {
+    for (int ldh : {0, 1, 2})
+      for (int sth : {0, 2, 3}) {
+        if (level < 2 && !((ldh == 2 && sth == 2) || (ldh == 0 && sth == 0) || (ldh == 2 && sth == 0) || (ldh == 0 && sth == 2))) continue;
+        Cfg c = baseline(op); c.vb = sh[0]; c.unroll = sh[1]; c.block = sh[2]; c.ldh = ldh; c.sth = sth;
+        v.push_back(c);
+      }
+  }
+  // 2. ldg + L2 prefetch ahead
+  for (auto& sh : shapes) {
+    if (level < 2 && sh[2] == 1024) continue;
+    for (int pf : {1, 2})
+      for (long long dist : {0ll, 1ll, 2ll, 4ll}) {   // in waves of resident blocks
+        for (int hint : {0, 2}) {
+          Cfg c = baseline(op); c.vb = sh[0]; c.unroll = sh[1]; c.block = sh[2]; c.ldh = hint; c.sth = hint; c.pf = pf;
+          const long long resident = (long long)g_sms * (2048 / c.block);
+          c.pfdist = dist * resident;
+          if (level < 2 && dist == 4) continue;
+          v.push_back(c);
+        }
+      }
+  }
+  // 3. staged, one tile per block
+  for (int tile : {2048, 4096, 8192, 16384, 32768})
+    for (int block : {128, 256, 512})
+      for (int bulkst : {0, 1})
+        for (int ef : {0, 1}) {
+          if (tile / 16 < block) continue;
+          Cfg c; c.kind = 1; c.op = op; c.tile = tile; c.block = block; c.stages = 1; c.grid = 0; c.bulk_store = bulkst;
+          c.sth = ef ? 2 : 0; c.ld_ef = ef; c.st_ef = ef;
+          v.push_back(c);
+        }
+  // 4. staged, persistent ring
+  for (int tile : {4096, 8192, 16384, 32768})
+    for (int stages : {2, 3, 4})
+      for (int grid : {1, 2, 4})
+        for (int block : {128, 256, 512})
+          for (int bulkst : {0, 1}) {
+            if (tile / 16 < block) continue;
+            const int nin = op == OP_COPY || op == OP_MUL ? 1 : op == OP_NSTREAM ? 3 : 2;
+            if ((long long)tile * stages * nin * grid > 200 * 1024) continue;
+            if (level < 2 && (long long)tile * stages * nin * grid < 48 * 1024) continue;  // too little in flight
+            Cfg c; c.kind = 1; c.op = op; c.tile = tile; c.block = block; c.stages = stages; c.grid = grid; c.bulk_store = bulkst;
+            c.sth = 2; c.ld_ef = 1; c.st_ef = 1;
+            v.push_back(c);
+          }
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------------
+static const double IA = 0.1, IB = 0.2, IC = 0.3, SC = 0.4;
+static void init_arrays(Arrays x, size_t n) {
+  fill_kernel<<<g_sms * 8, 512, 0, g_stream>>>(x.a, n, IA);
+  fill_kernel<<<g_sms * 8, 512, 0, g_stream>>>(x.b, n, IB);
+  fill_kernel<<<g_sms * 8, 512, 0, g_stream>>>(x.c, n, IC);
+  CK(cudaStreamSynchronize(g_stream));
+}
+static double expected(int op) {
+  switch (op) {
+    case OP_COPY: return IA;
+    case OP_MUL: return SC * IC;
+    case OP_ADD: return IA + IB;
+    case OP_TRIAD: return std::fma(SC, IC, IB);
+    default: return IA + std::fma(SC, IC, IB);
+  }
+}
+static double* out_of(Arrays x, int op) { return (op == OP_COPY || op == OP_ADD) ? x.c : op == OP_MUL ? x.b : x.a; }
+
+// run once on freshly initialised arrays with a poisoned output; count wrong elements
+static unsigned long long verify(const Launch& L, int op, Arrays x, size_t n, unsigned long long* d_bad) {
+  init_arrays(x, n);
+  if (op != OP_NSTREAM) CK(cudaMemsetAsync(out_of(x, op), 0xff, n * 8, g_stream));
+  CK(cudaMemsetAsync(d_bad, 0, 8, g_stream));
+  L.go();
+  const cudaError_t le = cudaGetLastError();
+  if (le != cudaSuccess) {
+    CK(cudaStreamSynchronize(g_stream));
+    init_arrays(x, n);
+    return ~0ull;  // the launch itself was refused
+  }
+  check_kernel<<<g_sms * 8, 512, 0, g_stream>>>(out_of(x, op), n, expected(op), d_bad);
+  unsigned long long bad = 0;
+  CK(cudaMemcpyAsync(&bad, d_bad, 8, cudaMemcpyDeviceToHost, g_stream));
+  CK(cudaStreamSynchronize(g_stream));
+  CK(cudaGetLastError());
+  init_arrays(x, n);
+  return bad;
+}
+
+static int op_by_name(const char* s) {
+  for (int i = 0; i < 5; i++) if (!std::strcmp(s, kOpName[i])) return i;
+  return -1;
+}
+// the kernel the driver runs just before `op` in --only All order: copy mul add triad dot nstream
+static int prev_op(int op) { return op == OP_COPY ? OP_NSTREAM : op == OP_MUL ? OP_COPY : op == OP_ADD ? OP_MUL : op == OP_TRIAD ? OP_ADD : -1 /* dot */; }
+
+using clk = std::chrono::steady_clock;
+
+static void mode_sweep(bool seq, int log2n, int op, int level) {
+  const size_t n = (size_t)1 << log2n;
+  Arrays x;
+  CK(cudaMalloc(&x.a, n * 8)); CK(cudaMalloc(&x.b, n * 8)); CK(cudaMalloc(&x.c, n * 8));
+  unsigned long long* d_bad; CK(cudaMalloc(&d_bad, 8));
+  double* d_out; CK(cudaMalloc(&d_out, 8));
+  init_arrays(x, n);
+  const double bytes = (double)kWeight[op] * 8.0 * (double)n;
+  const int reps = seq ? (log2n >= 28 ? 12 : 60) : (log2n >= 28 ? 10 : 60);
+  const int pop = prev_op(op);
+  Launch prevL;
+  if (pop >= 0) prevL = plan(baseline(pop), x, n, SC);
+  cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  std::printf("mode,op,log2n,gbs,us,bad,cfg\n");
+  for (const Cfg& c : candidates(op, level)) {
+    const Launch L = plan(c, x, n, SC);
+    if (!L.ok) continue;
+    const unsigned long long bad = verify(L, op, x, n, d_bad);
+    if (bad == ~0ull) { std::printf("%s,%s,%d,0,0,LAUNCH_REFUSED grid=%u block=%u smem=%u,\"%s\"\n", seq ? "seq" : "b2b", kOpName[op], log2n, L.grid, L.block, L.smem, c.str().c_str()); continue; }
+    double us;
+    if (!seq) {
+      for (int i = 0; i < 3; i++) L.go();
+      CK(cudaEventRecord(e0, g_stream));
+      for (int i = 0; i < reps; i++) L.go();
+      CK(cudaEventRecord(e1, g_stream));
+      CK(cudaStreamSynchronize(g_stream));
+      float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+      us = ms * 1e3 / reps;
+    } else {
+      double best = 1e30;
+      for (int i = 0; i < reps + 3; i++) {
+        if (pop >= 0) prevL.go();
+        else readsum_kernel<<<g_sms * 8, 512, 0, g_stream>>>(x.a, x.b, n, d_out);  // dot stand-in: reads a and b
+        CK(cudaStreamSynchronize(g_stream));
+        const auto t0 = clk::now();
+        L.go();
+        CK(cudaStreamSynchronize(g_stream));
+        const double t = std::chrono::duration<double, std::micro>(clk::now() - t0).count();
+        if (i >= 3) best = std::min(best, t);
+      }
+      us = best;
+    }
+    if (op == OP_NSTREAM) init_arrays(x, n);
+    std::printf("%s,%s,%d,%.1f,%.3f,%llu,\"%s\"\n", seq ? "seq" : "b2b", kOpName[op], log2n, bytes / us / 1e3, us, bad, c.str().c_str());
+    std::fflush(stdout);
+  }
+}
+
+template <class F>
+static void timeit(const char* name, int reps, F f) {
+  std::vector<double> t(reps);
+  for (int i = 0; i < 100; i++) f();
+  for (int i = 0; i < reps; i++) {
+    const auto t0 = clk::now();
+    f();
+    t[i] = std::chrono::duration<double, std::micro>(clk::now() - t0).count();
+  }
+  std::sort(t.begin(), t.end());
+  std::printf("%-64s min %7.3f  p10 %7.3f  median %7.3f  p90 %7.3f us\n", name, t[0], t[reps / 10], t[reps / 2], t[reps * 9 / 10]);
+}
+
+static void mode_lat() {
+  const int reps = 4000;
+  cudaStream_t nb, bl;
+  CK(cudaStreamCreateWithFlags(&nb, cudaStreamNonBlocking));
+  CK(cudaStreamCreate(&bl));
+  cudaEvent_t ev; CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  timeit("legacy default stream + cudaDeviceSynchronize (reference cuda model)", reps, [&] { empty_kernel<<<1, 32>>>(); cudaDeviceSynchronize(); });
+  timeit("legacy default stream + cudaStreamSynchronize(0)", reps, [&] { empty_kernel<<<1, 32>>>(); cudaStreamSynchronize(0); });
+  timeit("non-blocking stream + cudaStreamSynchronize", reps, [&] { empty_kernel<<<1, 32, 0, nb>>>(); cudaStreamSynchronize(nb); });
+  timeit("non-blocking stream + cudaDeviceSynchronize", reps, [&] { empty_kernel<<<1, 32, 0, nb>>>(); cudaDeviceSynchronize(); });
+  timeit("blocking stream + cudaStreamSynchronize", reps, [&] { empty_kernel<<<1, 32, 0, bl>>>(); cudaStreamSynchronize(bl); });
+  timeit("non-blocking stream + cudaStreamQuery spin", reps, [&] { empty_kernel<<<1, 32, 0, nb>>>(); while (cudaStreamQuery(nb) == cudaErrorNotReady) {} });
+  timeit("non-blocking stream + event record + cudaEventQuery spin", reps, [&] { empty_kernel<<<1, 32, 0, nb>>>(); cudaEventRecord(ev, nb); while (cudaEventQuery(ev) == cudaErrorNotReady) {} });
+  timeit("non-blocking stream + event record + cudaEventSynchronize", reps, [&] { empty_kernel<<<1, 32, 0, nb>>>(); cudaEventRecord(ev, nb); cudaEventSynchronize(ev); });
+  timeit("launch only (non-blocking stream)", reps, [&] { empty_kernel<<<1, 32, 0, nb>>>(); });
+  CK(cudaDeviceSynchronize());
+  // a CUDA graph of one kernel node
+  cudaGraph_t graph; cudaGraphExec_t exec;
+  CK(cudaStreamBeginCapture(nb, cudaStreamCaptureModeThreadLocal));
+  empty_kernel<<<1, 32, 0, nb>>>();
+  CK(cudaStreamEndCapture(nb, &graph));
+  CK(cudaGraphInstantiate(&exec, graph, 0));
+  timeit("graph launch (1 kernel node) + cudaStreamSynchronize", reps, [&] { cudaGraphLaunch(exec, nb); cudaStreamSynchronize(nb); });
+  // parameter-block size: 16 bytes vs 128 bytes makes no difference to an empty kernel; grid size does
+  for (unsigned grid : {148u, 1024u, 4096u, 32768u, 131072u}) {
+    char name[96];
+    std::snprintf(name, sizeof name, "empty kernel, grid %u x 128 threads + cudaStreamSynchronize", grid);
+    timeit(name, 2000, [&] { empty_kernel<<<grid, 128, 0, nb>>>(); cudaStreamSynchronize(nb); });
+  }
+  for (unsigned grid : {1024u, 8192u, 32768u}) {
+    char name[96];
+    std::snprintf(name, sizeof name, "empty kernel, grid %u x 512 threads + cudaStreamSynchronize", grid);
+    timeit(name, 2000, [&] { empty_kernel<<<grid, 512, 0, nb>>>(); cudaStreamSynchronize(nb); });
+  }
+}
+
+// the whole sequence with blocking calls at an L2-resident size; min per kernel
+static void mode_alt(int log2n) {
+  const size_t n = (size_t)1 << log2n;
+  double* d_out; CK(cudaMalloc(&d_out, 8));
+  struct Variant { const char* name; int vb, unroll, block, ldh, sth, order; };
+  const Variant vars[] = {
+      {"b200 shape (16B x4, 128 thr), alloc a b c", 16, 4, 128, 0, 0, 0},
+      {"b200 shape, alloc c b a", 16, 4, 128, 0, 0, 1},
+      {"b200 shape, no_allocate loads", 16, 4, 128, 1, 0, 0},
+      {"16B x2, 256 thr", 16, 2, 256, 0, 0, 0},
+      {"16B x1, 256 thr", 16, 1, 256, 0, 0, 0},
+      {"16B x1, 512 thr", 16, 1, 512, 0, 0, 0},
+      {"8B x4, 256 thr (reference-like work per thread)", 8, 4, 256, 0, 0, 0},
+      {"8B x2, 128 thr", 8, 2, 128, 0, 0, 0},
+      {"32B x1, 256 thr", 32, 1, 256, 0, 0, 0},
+      {"32B x2, 128 thr", 32, 2, 128, 0, 0, 0},
+  };
+  for (const Variant& v : vars) {
+    Arrays x;
+    if (v.order == 0) { CK(cudaMalloc(&x.a, n * 8)); CK(cudaMalloc(&x.b, n * 8)); CK(cudaMalloc(&x.c, n * 8)); }
+    else { CK(cudaMalloc(&x.c, n * 8)); CK(cudaMalloc(&x.b, n * 8)); CK(cudaMalloc(&x.a, n * 8)); }
+    init_arrays(x, n);
+    Launch L[5];
+    for (int op = 0; op < 5; op++) {
+      Cfg c = baseline(op); c.vb = v.vb; c.unroll = v.unroll; c.block = v.block; c.ldh = v.ldh; c.sth = v.sth;
+      L[op] = plan(c, x, n, SC);
+      if (!L[op].ok) { std::printf("cannot plan %s\n", v.name); return; }
+    }
+    double best[6] = {1e30, 1e30, 1e30, 1e30, 1e30, 1e30};
+    const int order[6] = {OP_COPY, OP_MUL, OP_ADD, OP_TRIAD, -1, OP_NSTREAM};
+    for (int it = 0; it < 300; it++) {
+      if (it % 50 == 0) init_arrays(x, n);
+      for (int k = 0; k < 6; k++) {
+        const auto t0 = clk::now();
+        if (order[k] >= 0) L[order[k]].go();
+        else readsum_kernel<<<g_sms * 2, 256, 0, g_stream>>>(x.a, x.b, n, d_out);
+        cudaStreamSynchronize(g_stream);
+        const double t = std::chrono::duration<double, std::micro>(clk::now() - t0).count();
+        if (it > 2) best[k] = std::min(best[k], t);
+      }
+    }
+    std::printf("alt 2^%d %-52s copy %6.2f mul %6.2f add %6.2f triad %6.2f dot* %6.2f nstream %6.2f us\n", log2n, v.name, best[0], best[1], best[2],
+                best[3], best[4], best[5]);
+    std::fflush(stdout);
+    CK(cudaFree(x.a)); CK(cudaFree(x.b)); CK(cudaFree(x.c));
+  }
+}
+
+static void launch_flag(cudaStream_t st, unsigned long long* ctr, unsigned long long* flag_dev, bool pdl) {
+  if (!pdl) { flag_kernel<<<1, 1, 0, st>>>(ctr, flag_dev); return; }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1); cfg.blockDim = dim3(1); cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, flag_kernel, ctr, flag_dev);
+}
+
+// How a blocking call is launched and how its completion is learnt, on the real kernel.
+static void mode_path(int log2n, int op) {
+  const size_t n = (size_t)1 << log2n;
+  Arrays x;
+  CK(cudaMalloc(&x.a, n * 8)); CK(cudaMalloc(&x.b, n * 8)); CK(cudaMalloc(&x.c, n * 8));
+  init_arrays(x, n);
+  Cfg c = baseline(op);
+  if (log2n <= 22) { c.vb = 16; c.unroll = 4; c.block = 128; c.ldh = 0; c.sth = 0; }
+  const Launch L = plan(c, x, n, SC);
+  if (!L.ok) { std::printf("cannot plan\n"); return; }
+  unsigned long long *ctr, *flag_host, *flag_dev;
+  CK(cudaMalloc(&ctr, 8)); CK(cudaMemset(ctr, 0, 8));
+  CK(cudaHostAlloc(&flag_host, 64, cudaHostAllocMapped)); *flag_host = 0;
+  CK(cudaHostGetDevicePointer(&flag_dev, flag_host, 0));
+  unsigned long long expect = 0;
+  auto spin = [&] {
+    ++expect;
+    const auto t0 = clk::now();
+    unsigned long spins = 0;
+    while (__atomic_load_n(flag_host, __ATOMIC_ACQUIRE) != expect) {
+      if ((++spins & 0xfffff) == 0 && std::chrono::duration<double>(clk::now() - t0).count() > 5.0) { std::fprintf(stderr, "flag timeout\n"); std::exit(3); }
+    }
+  };
+  const int reps = log2n >= 28 ? 60 : 1500;
+  char name[160];
+  auto label = [&](const char* what) { std::snprintf(name, sizeof name, "%s 2^%d %s", kOpName[op], log2n, what); return name; };
+  cudaStream_t bl; CK(cudaStreamCreate(&bl));
+  timeit(label("A  <<<>>> non-blocking stream + cudaStreamSynchronize"), reps, [&] { L.go(); cudaStreamSynchronize(g_stream); });
+  timeit(label("A' <<<>>> blocking stream + cudaStreamSynchronize"), reps, [&] { L.go(bl); cudaStreamSynchronize(bl); });
+  timeit(label("B  <<<>>> legacy stream + cudaDeviceSynchronize"), reps, [&] { L.go(0); cudaDeviceSynchronize(); });
+  // graphs
+  cudaGraph_t g1, g2, g3; cudaGraphExec_t x1, x2, x3;
+  CK(cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeThreadLocal)); L.go(); CK(cudaStreamEndCapture(g_stream, &g1));
+  CK(cudaGraphInstantiate(&x1, g1, 0));
+  timeit(label("C  graph(kernel) + cudaStreamSynchronize"), reps, [&] { cudaGraphLaunch(x1, g_stream); cudaStreamSynchronize(g_stream); });
+  timeit(label("C' graph(kernel) on blocking stream + cudaStreamSynchronize"), reps, [&] { cudaGraphLaunch(x1, bl); cudaStreamSynchronize(bl); });
+  timeit(label("D  <<<>>> + flag kernel + host spin"), reps, [&] { L.go(); launch_flag(g_stream, ctr, flag_dev, false); spin(); });
+  timeit(label("E  <<<>>> + flag kernel (PDL) + host spin"), reps, [&] { L.go(); launch_flag(g_stream, ctr, flag_dev, true); spin(); });
+  CK(cudaStreamSynchronize(g_stream));
+  CK(cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeThreadLocal)); L.go(); launch_flag(g_stream, ctr, flag_dev, false); CK(cudaStreamEndCapture(g_stream, &g2));
+  CK(cudaGraphInstantiate(&x2, g2, 0));
+  timeit(label("F  graph(kernel -> flag) + host spin"), reps, [&] { cudaGraphLaunch(x2, g_stream); spin(); });
+  CK(cudaStreamSynchronize(g_stream));
+  CK(cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeThreadLocal)); L.go(); launch_flag(g_stream, ctr, flag_dev, true);
+  const cudaError_t ce = cudaStreamEndCapture(g_stream, &g3);
+  if (ce == cudaSuccess && cudaGraphInstantiate(&x3, g3, 0) == cudaSuccess) {
+    timeit(label("G  graph(kernel -> flag, programmatic edge) + host spin"), reps, [&] { cudaGraphLaunch(x3, g_stream); spin(); });
+  } else {
+    std::printf("G  capture of a PDL launch failed: %s\n", cudaGetErrorString(ce)); (void)cudaGetLastError();
+  }
+  CK(cudaStreamSynchronize(g_stream));
+  CK(cudaGetLastError());
+}
+
+// The six-kernel step enqueued back to back (bench.py's device-timed `value`): plain launches vs programmatic
+// dependent launches vs one graph per step.
+static void mode_seq6(int log2n) {
+  const size_t n = (size_t)1 << log2n;
+  Arrays x;
+  CK(cudaMalloc(&x.a, n * 8)); CK(cudaMalloc(&x.b, n * 8)); CK(cudaMalloc(&x.c, n * 8));
+  double* d_out; CK(cudaMalloc(&d_out, 8));
+  init_arrays(x, n);
+  Launch L[5];
+  for (int op = 0; op < 5; op++) L[op] = plan(baseline(op), x, n, SC);
+  const int order[6] = {OP_COPY, OP_MUL, OP_ADD, OP_TRIAD, -1, OP_NSTREAM};
+  cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  const int K = 100;
+  const double step_bytes = 16.0 * 8.0 * (double)n;
+  auto dot_standin = [&](bool pdl) {
+    if (!pdl) { readsum_kernel<<<g_sms * 8, 512, 0, g_stream>>>(x.a, x.b, n, d_out); return; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(g_sms * 8); cfg.blockDim = dim3(512); cfg.stream = g_stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, readsum_kernel, (const double*)x.a, (const double*)x.b, n, d_out);
+  };
+  auto step = [&](bool pdl) {
+    for (int k = 0; k < 6; k++) {
+      if (order[k] < 0) dot_standin(pdl);
+      else if (pdl) L[order[k]].go_pdl();
+      else L[order[k]].go();
+    }
+  };
+  for (int mode = 0; mode < 3; mode++) {
+    init_arrays(x, n);
+    cudaGraphExec_t gx = nullptr;
+    if (mode == 2) {
+      cudaGraph_t g;
+      CK(cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeThreadLocal)); step(false); CK(cudaStreamEndCapture(g_stream, &g));
+      CK(cudaGraphInstantiate(&gx, g, 0));
+    }
+    for (int rep = 0; rep < 3; rep++) {
+      for (int i = 0; i < 5; i++) { if (gx) cudaGraphLaunch(gx, g_stream); else step(mode == 1); }
+      CK(cudaEventRecord(e0, g_stream));
+      for (int i = 0; i < K; i++) { if (gx) cudaGraphLaunch(gx, g_stream); else step(mode == 1); }
+      CK(cudaEventRecord(e1, g_stream));
+      CK(cudaStreamSynchronize(g_stream));
+      CK(cudaGetLastError());
+      float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+      std::printf("seq6 2^%d %-28s %8.2f us/step  %8.1f GB/s\n", log2n, mode == 0 ? "plain launches" : mode == 1 ? "programmatic dependent" : "one graph per step", ms * 1e3 / K, step_bytes / (ms / K) / 1e6);
+      init_arrays(x, n);
+    }
+  }
+}
+
+int main(int argc, char** argv) {
+  if (argc < 2) { std::fprintf(stderr, "usage: ew_lab b2b|seq <log2n> <op> <level> | lat | alt <log2n>\n"); return 1; }
+  CK(cudaSetDevice(0));
+  cudaSetDeviceFlags(cudaDeviceScheduleSpin);
+  cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, 0));
+  g_sms = p.multiProcessorCount;
+  CK(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+  const std::string mode = argv[1];
+  if (mode == "lat") { mode_lat(); return 0; }
+  if (mode == "alt") { mode_alt(argc > 2 ? atoi(argv[2]) : 20); return 0; }
+  if (mode == "seq6") { mode_seq6(argc > 2 ? atoi(argv[2]) : 25); return 0; }
+  if (mode == "path") { const int op = argc > 3 ? op_by_name(argv[3]) : OP_TRIAD; mode_path(argc > 2 ? atoi(argv[2]) : 25, op < 0 ? OP_TRIAD : op); return 0; }
+  if (argc < 5) { std::fprintf(stderr, "b2b/seq need <log2n> <op> <level>\n"); return 1; }
+  const int op = op_by_name(argv[3]);
+  if (op < 0) { std::fprintf(stderr, "unknown op %s\n", argv[3]); return 1; }
+  mode_sweep(mode == "seq", atoi(argv[2]), op, atoi(argv[4]));
+  return 0;
+}
