@@ -101,7 +101,7 @@ struct Shard {
     uint64_t gen = 0;            // ctx->tune_gen it was built under
     unsigned nlaunch = 0;        // kernel nodes (for b200_launch_count)
     bool bell = false;           // dot: built with the doorbell
-  } plans[B200_NUM_KERNELS];
+  } plans[B200_NUM_KERNELS][2];  // [kernel][sweep direction]
   void* mailbox = nullptr;       // p2p combine: kMaxPeers slots in this GPU's HBM, written by the peers
   int rank = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -115,6 +115,7 @@ struct Command {
   int kind = CMD_NONE;
   int kernel = 0;
   double s0 = 0, s1 = 0, s2 = 0;
+  int reverse = 0;                              // kernel: sweep the shard from the top down
   void* host[3] = {nullptr, nullptr, nullptr};  // read: destinations; write: sources
   int prefetch_to = 0;                          // CMD_PREFETCH: 0 = the shard's GPU, 1 = the CPU
 };
@@ -136,6 +137,8 @@ struct b200_ctx {
   int sync_mode = SYNC_AUTO;
   int caller_device = -1;    // the device that was current when b200_create was called; restored by create and destroy
   bool use_graphs = true;    // option launch=graph|direct
+  bool alternate = true;     // option sweep=alternate|forward: consecutive kernels sweep in opposite directions
+  int next_reverse = 0;      // direction of the next kernel call
   uint64_t tune_gen = 1;     // bumped by every option change: invalidates the cached plans
   // one process per GPU (b200_join_group): this context is rank group_rank of group_world
   int group_world = 1, group_rank = 0;
@@ -229,7 +232,9 @@ static bool use_doorbell(const b200_ctx* ctx, const Shard* s, int kernel) {
 // Launch one kernel on one shard (device already current).  No synchronisation.
 static int shard_launch(b200_ctx* ctx, Shard* s, const Command& cmd, const b200_doorbell* bell) {
   const int eb = ctx->elem_bytes;
-  const b200_launch_cfg* cfg = &ctx->tune[cmd.kernel];
+  b200_launch_cfg cfg_store = ctx->tune[cmd.kernel];
+  if (cmd.reverse) cfg_store.flags |= B200_LAUNCH_REVERSE;
+  const b200_launch_cfg* cfg = &cfg_store;
   void* st = s->stream;
   if (cmd.kernel == B200_DOT) {
     const bool single = ctx->ngpus == 1;
@@ -334,7 +339,7 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
     // Replay a plan whenever nothing in the parameter block changes from call to call.
     const bool replay = ctx->use_graphs && launches && !ctx->timing && !nccl_dot && !(bell && !is_dot);
     if (replay) {
-      Shard::Plan& p = s->plans[cmd.kernel];
+      Shard::Plan& p = s->plans[cmd.kernel][cmd.reverse ? 1 : 0];
       if (!p.exec || p.gen != ctx->tune_gen || p.s0 != cmd.s0 || p.s1 != cmd.s1 || p.s2 != cmd.s2 || p.bell != (bell != nullptr)) {
         if (int rc = build_plan(ctx, s, cmd, bell, &p)) return rc;
       }
@@ -464,6 +469,7 @@ static void parse_cfg_fields(b200_launch_cfg* c, const std::string& fields) {
       if (k == "vec") c->vec_bytes = v; else if (k == "unroll") c->unroll = v; else if (k == "block") c->block = v;
       else if (k == "grid") c->grid = v; else if (k == "hint") c->cache_hint = v; else if (k == "variant") c->variant = v;
       else if (k == "stages") c->stages = v; else if (k == "chunk") c->chunk_bytes = v; else if (k == "contract") c->contract = v;
+      else if (k == "keep") c->keep_mb = v; else if (k == "flags") c->flags = v;
     }
     pos = end + 1;
   }
@@ -477,7 +483,11 @@ static int kernel_by_name(const std::string& s) {
 
 static int apply_option(b200_ctx* ctx, const std::string& key, const std::string& val) {
   ctx->tune_gen++;  // whatever changes: the cached plans are rebuilt on their next use
-  if (key == "launch") {
+  if (key == "sweep") {
+    if (val != "alternate" && val != "forward") { set_error("sweep must be alternate or forward, got '%s'", val.c_str()); return B200_EINVAL; }
+    ctx->alternate = val == "alternate";
+    ctx->next_reverse = 0;
+  } else if (key == "launch") {
     if (val != "graph" && val != "direct") { set_error("launch must be graph or direct, got '%s'", val.c_str()); return B200_EINVAL; }
     ctx->use_graphs = val == "graph";
   } else if (key == "contract") {
@@ -644,10 +654,11 @@ void b200_destroy(b200_ctx* ctx) {
     if (s->stream) cudaStreamDestroy(s->stream);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
-    for (auto& p : s->plans) {
-      if (p.exec) cudaGraphExecDestroy(p.exec);
-      if (p.graph) cudaGraphDestroy(p.graph);
-    }
+    for (auto& per_kernel : s->plans)
+      for (auto& p : per_kernel) {
+        if (p.exec) cudaGraphExecDestroy(p.exec);
+        if (p.graph) cudaGraphDestroy(p.graph);
+      }
     if (!ctx->managed) { cudaFree(s->a); cudaFree(s->b); cudaFree(s->c); }
     cudaFree(s->dot_ws); cudaFree(s->dot_dev); cudaFree(s->mailbox); cudaFree(s->bell_ticket); cudaFree(s->seq_counters);
     if (s->dot_host) cudaFreeHost(s->dot_host);
@@ -692,7 +703,7 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
   if (cudaGetDevice(&ctx->caller_device) != cudaSuccess) { (void)cudaGetLastError(); ctx->caller_device = -1; }
 
   // options from the environment: BABELSTREAM_B200_<KEY>
-  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem", "launch"};
+  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem", "launch", "sweep"};
   for (const char* k : keys) {
     std::string env = "BABELSTREAM_B200_";
     for (const char* p = k; *p; p++) env += (char)toupper(*p);
@@ -892,6 +903,8 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
                               "cudaStreamQuery spin", "doorbell"};
   snprintf(line, sizeof line, "  wait: %s\n", sync_names[ctx->sync_mode + 1]);
   out += line;
+  out += ctx->alternate ? "  sweep: consecutive kernels walk the arrays in opposite directions (sweep=forward: always bottom-up)\n"
+                        : "  sweep: forward (always bottom-up)\n";
   out += ctx->use_graphs ? "  launch: every call replays a captured one-kernel CUDA graph (launch=direct: <<<>>>)\n"
                          : "  launch: direct (<<<>>> per call)\n";
   snprintf(buf, (size_t)buflen, "%s", out.c_str());
@@ -914,6 +927,7 @@ static int run_kernel(b200_ctx* ctx, int kernel, double s0, double s1, double s2
   if (int rc = managed_home(ctx)) return rc;
   Command cmd;
   cmd.kind = CMD_KERNEL; cmd.kernel = kernel; cmd.s0 = s0; cmd.s1 = s1; cmd.s2 = s2;
+  if (ctx->alternate) { cmd.reverse = ctx->next_reverse; ctx->next_reverse ^= 1; }
   return run_all(ctx, cmd);
 }
 

@@ -48,6 +48,9 @@ static int launch_dot_typed(const DotCall& call) {
   args.partials = call.workspace;
   args.result_dev = call.result_dev; args.result_host = call.result_host;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
+  args.tiles_per_block = call.tiles_per_block;
+  args.sweep.reverse = call.reverse ? 1u : 0u;
+  args.sweep.keep_from = call.keep_from;
   args.bell_flag = static_cast<unsigned long long*>(call.bell.flag); args.bell_seq = call.bell.seq;
   args.seq_counters = static_cast<unsigned long long*>(call.seq_counters);
   args.p2p.world = call.p2p_world; args.p2p.rank = call.p2p_rank; args.p2p.seq = call.p2p_seq;
@@ -61,7 +64,7 @@ static int launch_dot_typed(const DotCall& call) {
     // one block of 32 warps: warp g adds group g -- the same order as the ticket variant, whatever the grid
     if (int rc = launch_kernel(dot_final_kernel<T>, 1u, 1024, 0, call.stream, call.r.flags, static_cast<const T*>(call.workspace),
                                call.grid, static_cast<T*>(call.result_dev), static_cast<T*>(call.result_host), args.bell_flag,
-                               args.bell_seq))
+                               args.bell_seq, args.seq_counters))
       return rc;
   }
   return B200_OK;

@@ -63,6 +63,7 @@ void set_p2p_timeout_ns(unsigned long long ns);
 struct Resolved {
   int vec_bytes, unroll, block, cache_hint, variant, contract, stages, chunk_bytes;
   int flags;        // B200_LAUNCH_* bits
+  int keep_mb;      // MB of traffic at the END of the sweep whose lines stay in L2 (evict-first hint only); 0 = none
   int grid_policy;  // the cfg.grid convention: >0 exact, <0 per-SM, INT32_MAX one tile per block
 };
 
@@ -75,6 +76,9 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
                 Resolved* out);
 // grid size for `ntiles` tiles under the policy
 unsigned grid_for(int grid_policy, unsigned long long ntiles, int num_sms);
+// first tile/block (dispatch order) of the keep region: the last keep_mb MB of a sweep that moves `bytes_per_unit`
+// bytes per tile (elementwise) or per block (dot); ~0 when nothing is kept
+unsigned long long keep_from_for(int keep_mb, int cache_hint, unsigned long long units, double bytes_per_unit);
 
 // Contiguous shard g of ngpus with boundaries on multiples of align_bytes (128 for device memory,
 // b200_shard_range; 2 MiB for managed memory so that no page has two owners)
@@ -111,6 +115,8 @@ struct EwCall {
   unsigned grid;
   cudaStream_t stream;
   Bell bell;
+  bool reverse = false;                     // sweep from the top down (B200_LAUNCH_REVERSE)
+  unsigned long long keep_from = ~0ull;     // tiles (dispatch order) from here on keep their lines in L2
 };
 int launch_ew_init(const EwCall& call);
 int launch_ew_copy(const EwCall& call);
@@ -137,6 +143,9 @@ struct DotCall {
   Resolved r;
   Geometry g;
   unsigned grid;
+  unsigned tiles_per_block = 0;             // > 0: contiguous chunk per logical block; 0: grid-stride
+  bool reverse = false;
+  unsigned long long keep_from = ~0ull;     // blocks (dispatch order) from here on load with evict_normal
   cudaStream_t stream;
 };
 int launch_dot_impl(const DotCall& call);

@@ -89,14 +89,17 @@ template <> struct Words<32> { uint64_t w[4]; };
     asm volatile("ld.global" Q ".v4.b64 {%0,%1,%2,%3}, [%4];"                                                   \
                  : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2]), "=l"(r.w[3]) : "l"(p));
 
-// same, with an L2 cache-policy operand (VB < 32 only)
+// same, with an L2 cache-policy operand (a createpolicy register: the policy can change from tile to tile)
 #define B200_LD_BODY_POLICY(Q)                                                                                  \
   if constexpr (VB == 4)                                                                                        \
     asm volatile("ld.global" Q ".b32 %0, [%1], %2;" : "=r"(r.w[0]) : "l"(p), "l"(policy));                      \
   else if constexpr (VB == 8)                                                                                   \
     asm volatile("ld.global" Q ".b64 %0, [%1], %2;" : "=l"(r.w[0]) : "l"(p), "l"(policy));                      \
+  else if constexpr (VB == 16)                                                                                  \
+    asm volatile("ld.global" Q ".v2.b64 {%0,%1}, [%2], %3;" : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(p), "l"(policy)); \
   else                                                                                                          \
-    asm volatile("ld.global" Q ".v2.b64 {%0,%1}, [%2], %3;" : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(p), "l"(policy));
+    asm volatile("ld.global" Q ".v4.b64 {%0,%1,%2,%3}, [%4], %5;"                                               \
+                 : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2]), "=l"(r.w[3]) : "l"(p), "l"(policy));
 
 #define B200_ST_BODY(Q)                                                                                         \
   if constexpr (VB == 4)                                                                                        \
@@ -114,17 +117,43 @@ template <> struct Words<32> { uint64_t w[4]; };
     asm volatile("st.global" Q ".b32 [%0], %1, %2;" ::"l"(p), "r"(r.w[0]), "l"(policy) : "memory");             \
   else if constexpr (VB == 8)                                                                                   \
     asm volatile("st.global" Q ".b64 [%0], %1, %2;" ::"l"(p), "l"(r.w[0]), "l"(policy) : "memory");             \
+  else if constexpr (VB == 16)                                                                                  \
+    asm volatile("st.global" Q ".v2.b64 [%0], {%1,%2}, %3;" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]), "l"(policy) : "memory"); \
   else                                                                                                          \
-    asm volatile("st.global" Q ".v2.b64 [%0], {%1,%2}, %3;" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]), "l"(policy) : "memory");
+    asm volatile("st.global" Q ".v4.b64 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "l"(r.w[0]), "l"(r.w[1]), "l"(r.w[2]), \
+                 "l"(r.w[3]), "l"(policy) : "memory");
 
-// L2 evict-first policy register, needed by H_EVICT_FIRST accesses narrower than 256 bits
-template <int VB, int HINT>
-__device__ __forceinline__ uint64_t make_policy() {
-  uint64_t policy = 0;
-  if constexpr (HINT == H_EVICT_FIRST && VB < 32)
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+// L2 cache-policy registers.  H_EVICT_FIRST accesses carry one as an operand, so that the policy can differ
+// between the body of a sweep (evict-first: the line is not wanted again) and its last tiles (see SweepArgs).
+enum L2Policy : int { L2_EVICT_FIRST = 0, L2_EVICT_NORMAL = 1, L2_EVICT_LAST = 2 };
+template <int KIND>
+__device__ __forceinline__ uint64_t l2_policy() {
+  uint64_t policy;
+  if constexpr (KIND == L2_EVICT_FIRST) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  else if constexpr (KIND == L2_EVICT_NORMAL) asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(policy));
+  else asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(policy));
   return policy;
 }
+template <int VB, int HINT>
+__device__ __forceinline__ uint64_t make_policy() {
+  if constexpr (HINT == H_EVICT_FIRST) return l2_policy<L2_EVICT_FIRST>();
+  else return 0;
+}
+
+// The sweep: in which order a grid walks its tiles, and which of them keep their lines in L2.
+//   reverse    block p (dispatch order) handles tile ntiles-1-p: the arrays are swept from the top down.  Consecutive
+//              kernels of a sequence alternate the direction, so each one starts on the data its predecessor touched
+//              last -- the part that is still in the 126 MB L2 (output lines not yet written back, inputs just read).
+//   keep_from  tiles p >= keep_from (dispatch order, i.e. the END of the sweep) load with evict_normal and store with
+//              evict_last instead of evict_first, so that the successor finds them.  Only with H_EVICT_FIRST (the other
+//              hints keep everything by default); ~0 = no tile.  Measured on B200 (profiles/r02/lab_zigzag.txt):
+//              2^25 fp64, six-kernel sequence of blocking calls: 655 us forward -> 635 us alternating -> 627 us with
+//              the last 96 MB kept; at 2^27 and beyond keeping HURTS (the kept lines take write-combining room from the
+//              stream: +2.6 % at 2^29), alternating alone still gains 0.3-0.6 %.
+struct SweepArgs {
+  unsigned long long keep_from;
+  unsigned int reverse;
+};
 
 // READONLY: the array is not written by this kernel (-> .nc, the non-coherent path).
 template <int VB, int HINT, bool READONLY>
@@ -132,7 +161,6 @@ __device__ __forceinline__ Words<VB> ldg(const void* p, uint64_t policy = 0) {
   Words<VB> r;
   if constexpr (HINT == H_DEFAULT) { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_1_RO) } else { B200_LD_BODY(B200_LD_QUAL_1_RW) } }
   else if constexpr (HINT == H_NOALLOC) { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_2_RO) } else { B200_LD_BODY(B200_LD_QUAL_2_RW) } }
-  else if constexpr (HINT == H_EVICT_FIRST && VB == 32) { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_3_RO) } else { B200_LD_BODY(B200_LD_QUAL_3_RW) } }
   else if constexpr (HINT == H_EVICT_FIRST) { if constexpr (READONLY) { B200_LD_BODY_POLICY(B200_LD_QUAL_3P_RO) } else { B200_LD_BODY_POLICY(B200_LD_QUAL_3P_RW) } }
   else if constexpr (HINT == H_STREAM) { B200_LD_BODY(B200_LD_QUAL_4_RW) }
   else { if constexpr (READONLY) { B200_LD_BODY(B200_LD_QUAL_5_RO) } else { B200_LD_BODY(B200_LD_QUAL_5_RW) } }
@@ -144,7 +172,6 @@ template <int VB, int HINT>
 __device__ __forceinline__ void stg(void* p, const Words<VB>& r, uint64_t policy = 0) {
   if constexpr (HINT == H_DEFAULT) { B200_ST_BODY(B200_ST_QUAL_1) }
   else if constexpr (HINT == H_NOALLOC) { B200_ST_BODY(B200_ST_QUAL_2) }
-  else if constexpr (HINT == H_EVICT_FIRST && VB == 32) { B200_ST_BODY(B200_ST_QUAL_3) }
   else if constexpr (HINT == H_EVICT_FIRST) { B200_ST_BODY_POLICY(B200_ST_QUAL_3P) }
   else if constexpr (HINT == H_STREAM) { B200_ST_BODY(B200_ST_QUAL_4) }
   else { B200_ST_BODY(B200_ST_QUAL_5) }
@@ -256,6 +283,7 @@ struct EwArgs {
   unsigned long long ntiles;  // ceil(nvec / (blockDim.x * UNROLL))
   unsigned long long n;       // total elements
   unsigned int head;          // leading scalar elements
+  SweepArgs sweep;            // direction and L2 keep region
   Doorbell bell;              // flag == nullptr: none
 };
 
@@ -293,16 +321,21 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
   const unsigned long long nvec = args.nvec;
   const unsigned long long tile_vecs = (unsigned long long)blockDim.x * UNROLL;
 
-  const uint64_t policy = make_policy<VB, HINT>();
+  const uint64_t body_policy = make_policy<VB, HINT>();
   Elems<T, VB> init_a, init_b, init_c;
   if constexpr (OP == OP_INIT) {
 #pragma unroll
     for (int e = 0; e < EPV; e++) { init_a.v[e] = s0; init_b.v[e] = s1; init_c.v[e] = s2; }
   }
 
-  for (unsigned long long tile = blockIdx.x; tile < args.ntiles; tile += gridDim.x) {
+  for (unsigned long long ptile = blockIdx.x; ptile < args.ntiles; ptile += gridDim.x) {
+    const unsigned long long tile = args.sweep.reverse ? args.ntiles - 1 - ptile : ptile;
     const unsigned long long v0 = tile * tile_vecs + threadIdx.x;
     const bool full = (tile + 1) * tile_vecs <= nvec;  // block-uniform
+    uint64_t policy = body_policy, st_policy = body_policy;
+    if constexpr (HINT == H_EVICT_FIRST) {
+      if (ptile >= args.sweep.keep_from) { policy = l2_policy<L2_EVICT_NORMAL>(); st_policy = l2_policy<L2_EVICT_LAST>(); }
+    }
 
     Words<VB> wa[UNROLL], wb[UNROLL], wc[UNROLL];
     // 1. every load of the tile first
@@ -321,11 +354,11 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
       const unsigned long long v = v0 + (unsigned long long)j * blockDim.x;
       if (full || v < nvec) {
         if constexpr (OP == OP_INIT) {
-          stg<VB, HINT>(va + v * VB, pack<T, VB>(init_a), policy);
-          stg<VB, HINT>(vb + v * VB, pack<T, VB>(init_b), policy);
-          stg<VB, HINT>(vc + v * VB, pack<T, VB>(init_c), policy);
+          stg<VB, HINT>(va + v * VB, pack<T, VB>(init_a), st_policy);
+          stg<VB, HINT>(vb + v * VB, pack<T, VB>(init_b), st_policy);
+          stg<VB, HINT>(vc + v * VB, pack<T, VB>(init_c), st_policy);
         } else if constexpr (OP == OP_COPY) {
-          stg<VB, HINT>(vc + v * VB, wa[j], policy);
+          stg<VB, HINT>(vc + v * VB, wa[j], st_policy);
         } else {
           Elems<T, VB> ea, eb, ec, r;
           if constexpr (LA) ea = unpack<T, VB>(wa[j]);
@@ -338,9 +371,9 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
             else if constexpr (OP == OP_TRIAD) r.v[e] = axpy<FUSED>(s0, ec.v[e], eb.v[e]);
             else r.v[e] = add_rn(ea.v[e], axpy<FUSED>(s0, ec.v[e], eb.v[e]));  // nstream: a + (b + s*c)
           }
-          if constexpr (OP == OP_MUL) stg<VB, HINT>(vb + v * VB, pack<T, VB>(r), policy);
-          else if constexpr (OP == OP_ADD) stg<VB, HINT>(vc + v * VB, pack<T, VB>(r), policy);
-          else stg<VB, HINT>(va + v * VB, pack<T, VB>(r), policy);
+          if constexpr (OP == OP_MUL) stg<VB, HINT>(vb + v * VB, pack<T, VB>(r), st_policy);
+          else if constexpr (OP == OP_ADD) stg<VB, HINT>(vc + v * VB, pack<T, VB>(r), st_policy);
+          else stg<VB, HINT>(va + v * VB, pack<T, VB>(r), st_policy);
         }
       }
     }
@@ -374,7 +407,7 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
 // no address sees more than ~37 atomics and the critical path after the last block's loads is two
 // atomics and two one-warp sums.
 // ------------------------------------------------------------------------------------------------
-constexpr int kDotMaxBlocks = 4096;
+constexpr int kDotMaxBlocks = 16384;
 constexpr int kDotGroups = 32;
 constexpr int kDotTicketStride = 64;  // in 32-bit words: every ticket on its own 256-byte line
 // workspace layout in bytes (zero-initialised once by the caller; every launch leaves it zeroed again,
@@ -555,6 +588,12 @@ struct DotArgs {
   void* result_host;     // mapped pinned, may be null
   unsigned long long nvec, ntiles, n;
   unsigned int head;
+  // Work assignment.  tiles_per_block = k > 0: LOGICAL block L owns the contiguous tiles [L*k, (L+1)*k) and always adds
+  // them in ascending order; k = 0: grid-stride (tiles L, L+G, ...).  sweep.reverse maps dispatch index p to L = G-1-p,
+  // i.e. changes WHEN a chunk is read, never what a thread adds in which order: the result has the same bits in both
+  // directions.  Blocks p >= sweep.keep_from load with evict_normal (H_EVICT_FIRST only).
+  unsigned int tiles_per_block;
+  SweepArgs sweep;
   unsigned long long* bell_flag;  // doorbell (mapped pinned host word) rung after the result is stored, or nullptr
   unsigned long long bell_seq;
   // Sequence numbers kept ON THE DEVICE (LEVEL 2): when non-null, the doorbell value is ++seq_counters[0] and the
@@ -564,9 +603,9 @@ struct DotArgs {
   P2PArgs p2p;           // world <= 1: plain single-GPU dot
 };
 
-// 1024-thread blocks leave 64 registers per thread: not enough for the widest tiles
-// (2 operands x 128 bytes per thread), which therefore run with at most 512 threads.
-constexpr int dot_max_block(int vb, int unroll) { return vb * unroll >= 128 ? 512 : 1024; }
+// dot blocks have at most 512 threads: the streaming shapes are held to 42 registers so that three such blocks fit an
+// SM (launch bound 512 x 3), the widest tiles (2 operands x 128 bytes per thread) get the 128 registers they need.
+constexpr int dot_max_block(int vb, int unroll) { return (void)vb, (void)unroll, 512; }
 
 // MODE: how the block partials become the result
 enum DotMode : int { DOT_TWO_PASS = 0,    // partials only; dot_final_kernel follows
@@ -577,7 +616,9 @@ enum DotMode : int { DOT_TWO_PASS = 0,    // partials only; dot_final_kernel fol
 constexpr int dot_block_bound(int vb, int unroll, int mode) {
   return mode >= DOT_TICKET_P2P ? 512 : dot_max_block(vb, unroll);
 }
-constexpr int dot_min_blocks(int vb, int unroll, int mode) { return (mode >= DOT_TICKET_P2P && vb * unroll <= 32) ? 3 : 1; }
+// Three 512-thread blocks per SM need <= 42 registers; the once-per-launch tail (tickets, group sums, all-reduce) would
+// otherwise push the streaming shapes to 44-48 and cost a third of the occupancy (-3.5 % at 2^29).
+constexpr int dot_min_blocks(int vb, int unroll, int mode) { return (void)mode, vb * unroll <= 32 ? 3 : 1; }
 
 template <typename T, int VB, int UNROLL, int HINT, bool FUSED, int MODE>
 __global__ void __launch_bounds__(dot_block_bound(VB, UNROLL, MODE), dot_min_blocks(VB, UNROLL, MODE))
@@ -594,14 +635,19 @@ dot_kernel(const __grid_constant__ DotArgs args) {
   const unsigned long long nvec = args.nvec;
   const unsigned long long tile_vecs = (unsigned long long)blockDim.x * UNROLL;
 
-  const uint64_t policy = make_policy<VB, HINT>();
+  uint64_t policy = make_policy<VB, HINT>();
+  if constexpr (HINT == H_EVICT_FIRST) { if (blockIdx.x >= args.sweep.keep_from) policy = l2_policy<L2_EVICT_NORMAL>(); }
+  const unsigned lb = args.sweep.reverse ? gridDim.x - 1u - blockIdx.x : blockIdx.x;  // logical block
+  const unsigned long long k = args.tiles_per_block;
+  const unsigned long long first = k ? (unsigned long long)lb * k : lb, step = k ? 1ull : gridDim.x;
+  const unsigned long long last = k ? (first + k < args.ntiles ? first + k : args.ntiles) : args.ntiles;
   T acc[UNROLL][EPV];
 #pragma unroll
   for (int j = 0; j < UNROLL; j++)
 #pragma unroll
     for (int e = 0; e < EPV; e++) acc[j][e] = T(0);
 
-  for (unsigned long long tile = blockIdx.x; tile < args.ntiles; tile += gridDim.x) {
+  for (unsigned long long tile = first; tile < last; tile += step) {
     const unsigned long long v0 = tile * tile_vecs + threadIdx.x;
     const bool full = (tile + 1) * tile_vecs <= nvec;
     Words<VB> wa[UNROLL], wb[UNROLL];
@@ -634,8 +680,8 @@ dot_kernel(const __grid_constant__ DotArgs args) {
 #pragma unroll
     for (int e = 0; e < EPV; e++) sum = add_rn(sum, acc[j][e]);
 
-  // ragged edges, block 0 only
-  if (blockIdx.x == 0) {
+  // ragged edges, logical block 0 only
+  if (lb == 0) {
     const unsigned long long tail_begin = args.head + nvec * EPV;
     const unsigned long long edge = args.head + (args.n - tail_begin);
     if (threadIdx.x < edge) {
@@ -647,13 +693,13 @@ dot_kernel(const __grid_constant__ DotArgs args) {
 
   sum = block_sum(sum, scratch);
   T* const partials = static_cast<T*>(args.partials);
-  if (threadIdx.x == 0) partials[blockIdx.x] = sum;
+  if (threadIdx.x == 0) partials[lb] = sum;
 
   if constexpr (MODE != DOT_TWO_PASS) {
     char* const ws = reinterpret_cast<char*>(args.partials);
     unsigned int* const top_ticket = reinterpret_cast<unsigned int*>(ws + kDotWsTop);
     T* const gsums = reinterpret_cast<T*>(ws + kDotWsGroupSums);
-    const unsigned ng = dot_num_groups(gridDim.x), g = blockIdx.x % ng;
+    const unsigned ng = dot_num_groups(gridDim.x), g = lb % ng;
     unsigned int* const my_ticket = reinterpret_cast<unsigned int*>(ws + kDotWsGroupTickets) + g * kDotTicketStride;
     const unsigned gsize = (gridDim.x - g + ng - 1) / ng;  // blocks in my group
     if (threadIdx.x == 0) {
@@ -716,7 +762,7 @@ dot_collect_kernel(const __grid_constant__ P2PArgs p, T* result_dev, T* result_h
 template <typename T>
 __global__ void __launch_bounds__(1024)
 dot_final_kernel(const T* partials, unsigned nparts, T* result_dev, T* result_host, unsigned long long* bell_flag,
-                 unsigned long long bell_seq) {
+                 unsigned long long bell_seq, unsigned long long* seq_counters) {
   __shared__ T gs[kDotGroups];
   pdl_entry();
   const unsigned ng = dot_num_groups(nparts), w = threadIdx.x >> 5;
@@ -729,6 +775,7 @@ dot_final_kernel(const T* partials, unsigned nparts, T* result_dev, T* result_ho
     const unsigned lane = threadIdx.x;
     const T v = warp_sum(lane < ng ? gs[lane] : T(0));
     if (lane == 0) {
+      if (seq_counters) { bell_seq = seq_counters[0] + 1; seq_counters[0] = bell_seq; }  // see DotArgs::seq_counters
       if (result_dev) *result_dev = v;
       if (result_host) *result_host = v;
       if (bell_flag) ring_host(bell_flag, bell_seq);

@@ -37,6 +37,8 @@ int launch_ew_typed(const EwCall& call) {
   EwArgs args;
   args.a = call.a; args.b = call.b; args.c = call.c;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
+  args.sweep.reverse = call.reverse ? 1u : 0u;
+  args.sweep.keep_from = call.keep_from;
   args.bell.ticket = static_cast<unsigned int*>(call.bell.ticket);
   args.bell.flag = static_cast<unsigned long long*>(call.bell.flag);
   args.bell.seq = call.bell.seq;

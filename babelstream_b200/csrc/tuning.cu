@@ -28,7 +28,7 @@ const char* last_error_message() { return g_error; }
 int size_class(size_t n, int elem_bytes, int l2_bytes) {
   if (l2_bytes <= 0) l2_bytes = 126 << 20;
   const double f = 3.0 * (double)n * elem_bytes / (double)l2_bytes;
-  return f <= 0.8 ? SIZE_L2 : f <= 3.2 ? SIZE_KNEE : f <= 8.0 ? SIZE_HBM : SIZE_HBM_XL;
+  return f <= 0.8 ? SIZE_L2 : f <= 3.2 ? SIZE_KNEE : f <= 16.0 ? SIZE_HBM : SIZE_HBM_XL;
 }
 
 int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
@@ -50,15 +50,15 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   r.variant = B200_VARIANT_LDST;
   r.grid_policy = INT_MAX;  // one tile per block: always beats a persistent grid-stride loop (by 4-10 %)
   // ---- the per-size table (auto) ------------------------------------------------------------------
-  // Sources: round 1 tools/sweep.py (profiles/r01/sweep_f64.csv: 6560 shapes, back to back) and round 2
+  // Sources: round 1 tools/sweep.py (profiles/r01/sweep_f64_top.csv: 6560 shapes, back to back) and round 2
   // tools/lab/ew_lab (profiles/r02/lab_*.csv: blocking calls in the driver's kernel order, which is what
   // src/main.cpp times).  Four classes by the footprint F of the three arrays against the L2 size:
   //
   //   SIZE_L2     F <= 0.8 L2   launch-latency bound (8-20 us per call): fat threads in small blocks, default
   //                             cache policy so that consecutive kernels hit in L2
-  //   SIZE_KNEE   F <= 3.2 L2    part of every array still lives in L2 when the next kernel reads it: keep the
-  //                             lines (no evict-first), L1 no-allocate
-  //   SIZE_HBM    F <= 8 L2     HBM-bound, 50-250 us per call: ramp-up and tail are 3-4 % of the call, and they
+  //   SIZE_KNEE   F <= 3.2 L2    part of every array still lives in L2 when the next kernel reads it: same shape,
+  //                             default policy (no evict-first: the lines are wanted again)
+  //   SIZE_HBM    F <= 16 L2    HBM-bound, 50-250 us per call: ramp-up and tail are 3-4 % of the call, and they
   //                             shrink with the tile -- 4 KB per array per block (256 threads x 16 B) runs the
   //                             blocking call 2.3 us (triad, add) faster than 8 KB at 2^25 fp64 although both
   //                             stream at the same 7.0 TB/s back to back
@@ -72,7 +72,7 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   // register or bulk stores (the cub::DeviceTransform ublkcp shape), L2 prefetch ahead of the loads (per-line
   // prefetch.global.L2 -- what the reference's thrust model runs -- or cp.async.bulk.prefetch.L2), persistent
   // multi-stage rings: all within +-0.5 % of plain LDG/STG at 2^25 and 1-2.5 % slower at 2^29.
-  r.cache_hint = l2_resident ? B200_HINT_DEFAULT : cls == SIZE_KNEE ? B200_HINT_NOALLOC : B200_HINT_EVICT_FIRST;
+  r.cache_hint = cls <= SIZE_KNEE ? B200_HINT_DEFAULT : B200_HINT_EVICT_FIRST;
   switch (kernel) {
     case B200_COPY: case B200_MUL: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
     case B200_ADD: case B200_TRIAD:
@@ -85,19 +85,25 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
     case B200_DOT:
       // read-only: a bounded grid-stride grid (the partials must fit the workspace).  Tuned in the
       // driver's own situation -- blocking call, issued right after triad whose dirty lines are
-      // still draining from L2 (profiles/r01/sweep_dot_blocking_after_triad.csv): 8 blocks of 512
+      // still draining from L2 (profiles/r01/sweep_dot_blocking_after_triad_top.csv): 8 blocks of 512
       // threads per SM (two waves, the second balancing the first) with 2 x 16-byte loads per
       // operand in flight is within 1.1 % of the best shape at 2^25, 2^27 and 2^29; shapes with
       // less than full occupancy win in isolation but lose up to 10 % in sequence.
       r.variant = B200_VARIANT_DOT_TICKET;
       r.vec_bytes = 16; r.unroll = 2; r.block = 512; r.grid_policy = -8;
-      r.cache_hint = l2_resident ? B200_HINT_DEFAULT : B200_HINT_NOALLOC;
+      // evict-first where the end of the sweep is kept for the next kernel (SIZE_HBM), else L1 no-allocate only
+      r.cache_hint = l2_resident ? B200_HINT_DEFAULT : cls == SIZE_HBM ? B200_HINT_EVICT_FIRST : B200_HINT_NOALLOC;
       break;
   }
-  if (l2_resident) {
-    // Working set inside L2 (<= 2^22 doubles): driver-timed candidates at 2^20..2^22,
-    // profiles/r01/small_size_candidates.txt and profiles/r02/lab_alt.txt
-    if (kernel == B200_DOT) { r.vec_bytes = 32; r.unroll = 4; r.block = 256; r.grid_policy = -2; }
+  // The last 96 MB of a sweep stay in L2 for the next kernel -- only where that pays (see SweepArgs in kernels.cuh)
+  r.keep_mb = (cls == SIZE_HBM && r.cache_hint == B200_HINT_EVICT_FIRST) ? 96 : 0;
+  if (cls <= SIZE_KNEE) {
+    // Working set inside L2 (<= 2^22 doubles) or not much larger (2^23, 2^24): one 32-byte access per thread in
+    // 256-thread blocks.  Driver-timed candidates: profiles/r01/small_size_candidates.txt (2^20..2^22),
+    // profiles/r02/class_calibration.txt (2^20..2^24: at the knee the six-kernel step takes 181.6 us with this
+    // shape and default policy against 189.6 us with the HBM shapes + no-allocate and 229.6 us for cuda-stream
+    // at 2^23; dot alone 28.3 vs 33.5 us because triad's output stays in L2 for it).
+    if (kernel == B200_DOT) { if (l2_resident) { r.vec_bytes = 32; r.unroll = 4; r.block = 256; r.grid_policy = -2; } }
     else { r.vec_bytes = 32; r.unroll = 1; r.block = 256; }
   }
   r.contract = 1;
@@ -115,6 +121,7 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   if (c.stages) r.stages = c.stages;
   if (c.chunk_bytes) r.chunk_bytes = c.chunk_bytes;
   r.flags = c.flags;
+  if (c.keep_mb) r.keep_mb = c.keep_mb < 0 ? 0 : c.keep_mb;
 
   // ---- validation ----
   if (r.vec_bytes != 8 && r.vec_bytes != 16 && r.vec_bytes != 32 && r.vec_bytes != elem_bytes) {
@@ -124,7 +131,7 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   const bool unroll_ok = r.unroll == 1 || r.unroll == 2 || r.unroll == 4 || (r.unroll == 8 && r.vec_bytes == 16);
   if (!unroll_ok) { set_error("unroll must be 1, 2, 4 (or 8 with 16-byte vectors), got %d", r.unroll); return B200_EINVAL; }
   // register budget: see ew_max_block / dot_max_block in kernels.cuh
-  const int max_block = kernel == B200_DOT ? (r.vec_bytes * r.unroll >= 128 ? 512 : 1024)
+  const int max_block = kernel == B200_DOT ? 512
                                            : (r.vec_bytes * r.unroll <= 32 ? 1024 : 512);
   if (r.block < 32 || r.block > max_block || r.block % 32) {
     set_error("block must be a multiple of 32 in [32, %d] for vec_bytes=%d unroll=%d, got %d", max_block, r.vec_bytes,
@@ -159,6 +166,13 @@ unsigned grid_for(int grid_policy, unsigned long long ntiles, int num_sms) {
   if (g > 0x7fffffffull) g = 0x7fffffffull;  // gridDim.x limit; the tile loop covers the rest
   if (g == 0) g = 1;
   return (unsigned)g;
+}
+
+unsigned long long keep_from_for(int keep_mb, int cache_hint, unsigned long long units, double bytes_per_unit) {
+  if (keep_mb <= 0 || cache_hint != B200_HINT_EVICT_FIRST || units == 0 || !(bytes_per_unit > 0)) return ~0ull;
+  const double want = (double)keep_mb * 1048576.0 / bytes_per_unit;
+  const unsigned long long keep = want >= (double)units ? units : (unsigned long long)want;
+  return units - keep;
 }
 
 Geometry make_geometry(const void* p0, const void* p1, const void* p2, size_t n, int elem_bytes, int vec_bytes,
@@ -229,7 +243,7 @@ int b200_resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_b
     memset(out, 0, sizeof *out);
     out->vec_bytes = r.vec_bytes; out->unroll = r.unroll; out->block = r.block; out->grid = r.grid_policy;
     out->cache_hint = r.cache_hint; out->variant = r.variant; out->contract = r.contract;
-    out->stages = r.stages; out->chunk_bytes = r.chunk_bytes; out->flags = r.flags;
+    out->stages = r.stages; out->chunk_bytes = r.chunk_bytes; out->flags = r.flags; out->keep_mb = r.keep_mb;
   }
   if (grid_out) {
     // geometry for perfectly aligned arrays

@@ -26,6 +26,8 @@ WEIGHTS = {"copy": 2, "mul": 2, "add": 3, "triad": 3, "dot": 2, "nstream": 4, "i
 HINTS = {"auto": 0, "default": 1, "noalloc": 2, "evict_first": 3, "stream": 4, "prefetch": 5}
 VARIANTS = {"auto": 0, "ldst": 1, "bulk": 2, "tma": 3, "two_pass": 1, "ticket": 2}
 LAUNCH_PDL = 1   # B200_LAUNCH_PDL: programmatic dependent launch (cfg.flags)
+LAUNCH_REVERSE = 2          # B200_LAUNCH_REVERSE: sweep the arrays from the top down
+LAUNCH_DOT_GRIDSTRIDE = 4   # B200_LAUNCH_DOT_GRIDSTRIDE: dot with the round-1 grid-stride assignment
 ETIMEOUT = -7    # B200_ETIMEOUT
 
 START_A, START_B, START_C, START_SCALAR = 0.1, 0.2, 0.0, 0.4  # src/Stream.h:24-27
@@ -44,7 +46,8 @@ class LaunchCfg(C.Structure):
     """b200_launch_cfg.  All zero = auto."""
     _fields_ = [("vec_bytes", C.c_int), ("unroll", C.c_int), ("block", C.c_int), ("grid", C.c_int),
                 ("cache_hint", C.c_int), ("variant", C.c_int), ("contract", C.c_int), ("stages", C.c_int),
-                ("chunk_bytes", C.c_int), ("flags", C.c_int), ("reserved", C.c_int * 2)]
+                ("chunk_bytes", C.c_int), ("flags", C.c_int), ("keep_mb", C.c_int),
+                ("reserved", C.c_int * 1)]
 
     @classmethod
     def make(cls, **kw) -> "LaunchCfg":

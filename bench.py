@@ -16,7 +16,8 @@ kernels cannot be served from cache; that is the `l2` statement in `config`.
 value   = algorithmic bytes of all ranks per step (16 * 8 * n * N, weights of src/benchmark.h:33-38)
           / device time per step: two CUDA events on the launching stream around the K timed steps,
           arrays resident in HBM, kernels enqueued back to back through LEVEL 1 of the C ABI with
-          programmatic dependent launch (cfg.flags = B200_LAUNCH_PDL), max over ranks.
+          programmatic dependent launch (cfg.flags = B200_LAUNCH_PDL) and alternating sweep direction
+          (B200_LAUNCH_REVERSE on every other launch, what LEVEL 2 does by default), max over ranks.
 kernels = per-kernel GB/s from a SECOND timed region of K steps with an event at every kernel boundary
           (an event between two kernels forbids their overlap, so this region runs without PDL and its
           step time is reported as `value_with_kernel_events`).  `roofline` is triad's average launch
@@ -430,7 +431,15 @@ def main():
             torch.cuda.current_stream().wait_event(ev_collected)
             pending[0] = None
 
-    def enqueue(kernel, cfg):
+    # Consecutive kernels sweep the arrays in opposite directions (B200_LAUNCH_REVERSE), as LEVEL 2 does by default:
+    # each kernel starts on the data its predecessor touched last, i.e. on what is still in L2.
+    sweep = [0]
+    cfgs = {(p, r): bs.LaunchCfg.make(flags=(bs.LAUNCH_PDL if p else 0) | (bs.LAUNCH_REVERSE if r else 0))
+            for p in (0, 1) for r in (0, 1)}
+
+    def enqueue(kernel, pdl_on):
+        cfg = cfgs[(1 if pdl_on else 0, sweep[0])]
+        sweep[0] ^= 1
         if kernel == "dot" and combine == "p2p":
             # Nothing later in the step depends on the sum, so the all-reduce is split: the dot kernel SENDS
             # its partial to every peer's mailbox over NVLink and returns; a one-warp kernel on a side stream
@@ -470,12 +479,11 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    pdl = bs.LaunchCfg.make(flags=bs.LAUNCH_PDL)
     # ---- device-timed region A: `value` ---------------------------------------------------------
     bs.launch("init", pa, pb, pc, n, eb, stream=st)
     for _ in range(W):
         for k in KERNEL_ORDER:
-            enqueue(k, pdl)
+            enqueue(k, True)
     collect()
     barrier()
     sampler = ClockSampler(local)
@@ -490,7 +498,7 @@ def main():
     ev_a0.record()
     for _ in range(K):
         for k in KERNEL_ORDER:
-            enqueue(k, pdl)
+            enqueue(k, True)
     ev_a1.record()
     finish_pending(ev_a1)
     torch.cuda.synchronize()
@@ -507,7 +515,7 @@ def main():
     i = 1
     for _ in range(K):
         for k in KERNEL_ORDER:
-            enqueue(k, None)
+            enqueue(k, False)
             ev[i].record()
             i += 1
     finish_pending(ev[-1])

@@ -62,8 +62,8 @@ enum { B200_VARIANT_AUTO = 0,
 typedef struct b200_launch_cfg {
   int vec_bytes;  /* 0 auto | 8 = 64-bit | 16 = 128-bit | 32 = 256-bit accesses (4: float scalar path) */
   int unroll;     /* 0 auto | 1,2,4,8 vectors per thread per tile (8 only with 16-byte vectors) */
-  int block;      /* 0 auto | threads per block, multiple of 32: up to 1024 while vec_bytes*unroll <= 32
-                     (dot: < 128), else up to 512 */
+  int block;      /* 0 auto | threads per block, multiple of 32: up to 1024 while vec_bytes*unroll <= 32, else up to
+                     512; dot: up to 512 */
   int grid;       /* 0 auto | >0 exact block count (grid-stride) | <0: -k means k blocks per SM |
                      INT32_MAX: one tile per block */
   int cache_hint; /* B200_HINT_* */
@@ -72,8 +72,10 @@ typedef struct b200_launch_cfg {
                      2 unfused: round(s*c) then add, the reference built -ffp-contract=off */
   int stages;     /* bulk/tma copy: ring depth (0 auto) */
   int chunk_bytes;/* bulk/tma copy: bytes per stage (0 auto) */
-  int flags;      /* B200_LAUNCH_* bits (LEVEL 1 only) */
-  int reserved[2];
+  int flags;      /* B200_LAUNCH_* bits */
+  int keep_mb;    /* 0 auto | -1 none | > 0: MB of traffic at the END of the sweep whose lines are kept in L2 (loads
+                     evict_normal, stores evict_last instead of evict_first) for the next kernel; evict-first hint only */
+  int reserved[1];
 } b200_launch_cfg;
 
 /* flags */
@@ -81,6 +83,12 @@ typedef struct b200_launch_cfg {
                              the stream has drained; it waits (griddepcontrol.wait) for that kernel's completion and
                              memory before its first access, so stream-order semantics are unchanged.  Removes the
                              ~2 us drain-and-launch gap between back-to-back kernels of an asynchronous sequence. */
+#define B200_LAUNCH_REVERSE 2 /* sweep the arrays from the top down (block p handles tile ntiles-1-p).  Results are
+                             bit-identical in both directions, dot included.  A caller that alternates the direction of
+                             consecutive kernels lets each one start on the data its predecessor touched last, i.e. on
+                             what is still in the 126 MB L2; LEVEL 2 does so by default (option sweep=alternate). */
+#define B200_LAUNCH_DOT_GRIDSTRIDE 4 /* dot: round-1 work assignment (block b adds tiles b, b+G, ...) instead of one
+                             contiguous chunk per block; different summation order, hence different low-order bits */
 
 /* ------------------------------------------------------------------------------------------
  * LEVEL 0 -- library / device queries (replace listDevices / getDeviceName / getDeviceDriver,
@@ -243,7 +251,11 @@ int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes);
  * pagefault = the reference's MEM=PAGEFAULT build, CUDAStream.cu:39-40: one 2 MiB-aligned system allocation
  * per array that the GPUs reach through page faults (HMM/ATS); B200_EUNSUPPORTED where
  * cudaDevAttrPageableMemoryAccess is 0),
- * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk) */
+ * launch=graph|direct (graph, the default: every call replays a one-kernel CUDA graph captured on first use --
+ * cudaGraphLaunch + wait returns 2.0-2.5 us sooner than <<<>>> + wait on B200),
+ * sweep=alternate|forward (alternate, the default: consecutive kernel calls sweep the arrays in opposite directions,
+ * see B200_LAUNCH_REVERSE),
+ * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk keep flags) */
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
 int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */
 

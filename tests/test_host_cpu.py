@@ -118,7 +118,8 @@ def test_resolve_cfg_size_classes():
         t, _ = bs.resolve_cfg("triad", 1 << log2n, 8, num_sms=148, l2_bytes=l2)
         shapes[log2n] = (t.vec_bytes, t.unroll, t.block, t.cache_hint)
     assert shapes[20] == shapes[22] and shapes[20][3] == bs.HINTS["default"], "L2-resident: default cache policy"
-    assert shapes[23][3] == bs.HINTS["noalloc"] and shapes[24][3] == bs.HINTS["noalloc"], "knee: keep the lines in L2"
+    assert shapes[23][3] == bs.HINTS["default"] and shapes[24][3] == bs.HINTS["default"], "knee: keep the lines in L2"
+    assert shapes[25] == shapes[26] and shapes[27] == shapes[29], "the tile grows between 2^26 and 2^27 (fp64)"
     assert shapes[25][3] == bs.HINTS["evict_first"] and shapes[29][3] == bs.HINTS["evict_first"], "HBM-bound: evict-first"
     tile = lambda s: s[0] * s[1] * s[2]
     assert tile(shapes[25]) < tile(shapes[29]), "short HBM-bound calls run smaller tiles (ramp-up and tail) than 2^29"
@@ -136,7 +137,9 @@ def test_resolve_cfg_kernel_specific_rules():
     with pytest.raises(bs.B200Error):
         bs.resolve_cfg("triad", 1 << 20, 8, cfg=bs.LaunchCfg.make(variant="tma"))   # only copy has async variants
     bs.resolve_cfg("copy", 1 << 20, 8, cfg=bs.LaunchCfg.make(variant="tma"))
-    bs.resolve_cfg("dot", 1 << 20, 8, cfg=bs.LaunchCfg.make(block=1024, vec_bytes=16, unroll=2))
+    bs.resolve_cfg("dot", 1 << 20, 8, cfg=bs.LaunchCfg.make(block=512, vec_bytes=16, unroll=2))
+    with pytest.raises(bs.B200Error):   # dot blocks stop at 512 threads (three of them per SM, register-capped)
+        bs.resolve_cfg("dot", 1 << 20, 8, cfg=bs.LaunchCfg.make(block=1024, vec_bytes=16, unroll=2))
     with pytest.raises(bs.B200Error):
         bs.resolve_cfg("dot", 1 << 20, 2)
 

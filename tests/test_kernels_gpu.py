@@ -205,12 +205,15 @@ def test_dot_variants_agree_bitwise(dtype):
     for v, us in ((8, (1, 2, 4)), (16, (1, 2, 4, 8)), (32, (1, 2, 4))):
         for u in us:
             for h in (1, 2, 3, 4, 5):
-                for blk, g in ((256, -2), (512, 7), (1024 if v * u < 128 else 512, -1)):
+                for blk, g, fl in ((256, -2, 0), (512, 7, bs.LAUNCH_DOT_GRIDSTRIDE), (128, -1, 0), (512, -40, 0)):
                     kw = dict(vec_bytes=v, unroll=u, cache_hint=h, block=blk, grid=g)
-                    r1 = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(variant="two_pass", **kw))[0]
-                    r2 = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(variant="ticket", **kw))[0]
+                    r1 = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(variant="two_pass", flags=fl, **kw))[0]
+                    r2 = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(variant="ticket", flags=fl, **kw))[0]
                     assert r1.tobytes() == r2.tobytes(), kw
                     assert abs(float(r1) - exact) <= 8 * eps * 20 * scale, kw
+                    # the sweep direction (and the L2 keep region) changes WHEN a chunk is read, never the bits
+                    r3 = gpu_dot(a0, b0, cfg=bs.LaunchCfg.make(variant="ticket", flags=fl | bs.LAUNCH_REVERSE, keep_mb=1, **kw))[0]
+                    assert r3.tobytes() == r2.tobytes(), kw
 
 
 def test_dot_misaligned_and_empty(orc):
@@ -412,3 +415,22 @@ def test_programmatic_dependent_launch_sequence_bit_exact(orc, dtype):
             assert (arr.cpu().numpy().view(u) == np.asarray(gold).view(u)).all(), n
         eps = np.finfo(dtype).eps
         assert abs(float(out.item()) - float(g[3])) <= 64 * eps * abs(float(g[3]))
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("kern", EW + ["init"])
+def test_sweep_direction_and_keep_region_bit_exact(orc, kern, dtype):
+    """B200_LAUNCH_REVERSE walks the tiles from the top down, keep_mb switches the cache policy of the last tiles of the
+    sweep: neither may change a bit, for any size (ragged edges are handled by logical tile, not by block index)."""
+    for n in (1, 33, 4097, 65536 + 7, (1 << 21) + 3):
+        a0, b0, c0 = rand(n, dtype, 11), rand(n, dtype, 12), rand(n, dtype, 13)
+        want = [a0.copy(), b0.copy(), c0.copy()]
+        oracle_apply(orc, kern, *want, True)
+        for flags in (0, bs.LAUNCH_REVERSE):
+            for keep in (-1, 1, 4096):
+                for shape in (dict(vec_bytes=16, unroll=1, block=256), dict(vec_bytes=32, unroll=2, block=128),
+                              dict(vec_bytes=8, unroll=4, block=512, grid=-2)):
+                    cfg = bs.LaunchCfg.make(cache_hint="evict_first", flags=flags, keep_mb=keep, **shape)
+                    got = gpu_apply(kern, a0, b0, c0, cfg=cfg)
+                    for g, w in zip(got, want):
+                        assert same_bits(g, w), (kern, n, flags, keep, shape)

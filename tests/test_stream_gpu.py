@@ -128,6 +128,7 @@ def test_options_and_variants(orc):
     for opts in ({}, {"copy_variant": "bulk"}, {"copy_variant": "tma"}, {"dot_variant": "two_pass"},
                  {"sync": "spin"}, {"sync": "stream"}, {"sync": "doorbell"}, {"sync": "doorbell", "dot_variant": "two_pass"},
                  {"launch": "direct"}, {"launch": "direct", "sync": "doorbell"}, {"launch": "graph", "dot_variant": "two_pass"},
+                 {"sweep": "forward"}, {"sweep": "forward", "launch": "direct"}, {"tune": "all:keep=-1"}, {"tune": "all:hint=3,keep=2;dot:hint=3,keep=1"},
                  {"timing": "1"}, {"timing": "1", "sync": "doorbell"}, {"tune": "all:vec=16,unroll=4,hint=3,grid=-4;dot:vec=32,unroll=2,block=256"}):
         with bs.B200Stream(n, dtype=np.float64, **opts) as s:
             total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)

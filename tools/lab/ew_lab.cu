@@ -130,7 +130,17 @@ struct LdgArgs {
   double s;
   int pf;                  // 0 none, 1 per-thread prefetch.global.L2 of the lines, 2 bulk prefetch by one thread
   unsigned long long pfdist;  // tiles ahead (0 = the tile about to be loaded)
+  int reverse;             // 1: block p handles tile ntiles-1-p (the grid sweeps the arrays from the top down)
+  unsigned long long keep_from;  // tiles p >= keep_from (processing order) use keep_policy instead of evict_first
+  int keep_mode;           // 0 none, 1 evict_normal on loads+stores, 2 evict_normal loads + evict_last stores, 3 stores only evict_last
 };
+__device__ __forceinline__ unsigned long long make_pol(int kind) {  // 0 evict_first 1 evict_normal 2 evict_last
+  unsigned long long p;
+  if (kind == 0) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  else if (kind == 1) asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+  else asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
 
 __device__ __forceinline__ void prefetch_line(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p) : "memory"); }
 __device__ __forceinline__ void prefetch_bulk(const void* p, unsigned bytes) {
@@ -143,11 +153,17 @@ ldg_kernel(const LdgArgs g) {
   using U = Uses<OP>;
   pdl_entry();
   constexpr int EPV = VB / 8;
-  const unsigned long long pol = (LDH == 2 || STH == 2) ? evict_first_policy() : 0ull;
+  const unsigned long long pol0 = (LDH == 2 || STH == 2) ? evict_first_policy() : 0ull;
   const unsigned long long tile_vecs = (unsigned long long)blockDim.x * UNROLL;
   char* const pa = arr(g.x, 0); char* const pb = arr(g.x, 1); char* const pc = arr(g.x, 2);
   char* const po = arr(g.x, U::OUT);
-  for (unsigned long long tile = blockIdx.x; tile < g.ntiles; tile += gridDim.x) {
+  for (unsigned long long ptile = blockIdx.x; ptile < g.ntiles; ptile += gridDim.x) {
+    const unsigned long long tile = g.reverse ? g.ntiles - 1 - ptile : ptile;
+    unsigned long long pol = pol0, spol = pol0;
+    if (g.keep_mode && ptile >= g.keep_from) {
+      pol = g.keep_mode == 3 ? pol0 : make_pol(1);
+      spol = g.keep_mode == 1 ? make_pol(1) : make_pol(2);
+    }
     if (g.pf) {
       const unsigned long long pt = tile + g.pfdist;
       if (pt < g.ntiles) {
@@ -189,7 +205,7 @@ ldg_kernel(const LdgArgs g) {
           const double c = U::C ? __longlong_as_double((long long)wc[j].w[e]) : 0.0;
           r.w[e] = (unsigned long long)__double_as_longlong(apply<OP>(a, b, c, g.s));
         }
-        st<VB, STH>(po + v * VB, r, pol);
+        st<VB, STH>(po + v * VB, r, spol);
       }
     }
   }
@@ -330,6 +346,23 @@ __global__ void readsum_kernel(const double* a, const double* b, size_t n, doubl
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) acc += a[i] * b[i];
   if (acc == 1.2345e300) *out = acc;
 }
+// dot stand-in with a sweep direction: one 32 KB chunk pair per block, blocks dispatched in order
+__global__ void __launch_bounds__(512) readsum_dir_kernel(const double* a, const double* b, size_t nchunks, int reverse, size_t keep_from, int keep_mode, double* out) {
+  const size_t p = blockIdx.x;
+  const size_t chunk = reverse ? nchunks - 1 - p : p;
+  const unsigned long long pol = (keep_mode && p >= keep_from) ? make_pol(1) : make_pol(0);
+  const char* pa = reinterpret_cast<const char*>(a) + chunk * 32768 + threadIdx.x * 16;
+  const char* pb = reinterpret_cast<const char*>(b) + chunk * 32768 + threadIdx.x * 16;
+  W<16> wa[4], wb[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) { wa[j] = ld<16, 2, true>(pa + j * 8192, pol); wb[j] = ld<16, 2, true>(pb + j * 8192, pol); }
+  double acc = 0;
+#pragma unroll
+  for (int j = 0; j < 4; j++)
+    acc += __longlong_as_double((long long)wa[j].w[0]) * __longlong_as_double((long long)wb[j].w[0]) +
+           __longlong_as_double((long long)wa[j].w[1]) * __longlong_as_double((long long)wb[j].w[1]);
+  if (acc == 1.2345e300) *out = acc;
+}
 __global__ void empty_kernel() {}
 // completion flag: bumps a device counter and stores it to a word of mapped pinned host memory
 __global__ void flag_kernel(unsigned long long* ctr, unsigned long long* host_flag) {
@@ -428,6 +461,7 @@ static Launch plan(const Cfg& c, Arrays x, size_t n, double s) {
     if (!L.lf) return L;
     if (c.block > (c.vb * c.unroll <= 32 ? 1024 : 512)) return L;
     L.la.x = x; L.la.s = s; L.la.pf = c.pf; L.la.pfdist = (unsigned long long)c.pfdist;
+    L.la.reverse = 0; L.la.keep_from = ~0ull; L.la.keep_mode = 0;
     L.la.nvec = n * 8 / c.vb;
     const unsigned long long tv = (unsigned long long)c.block * c.unroll;
     L.la.ntiles = (L.la.nvec + tv - 1) / tv;
@@ -841,6 +875,79 @@ static void mode_seq6(int log2n) {
   }
 }
 
+// "zigzag": consecutive kernels sweep the arrays in opposite directions, and the last part of every sweep keeps its
+// lines in L2 (no evict-first), so that the next kernel starts on the data the previous one touched last.
+static void mode_zz(int log2n, int only_triad) {
+  const size_t n = (size_t)1 << log2n;
+  Arrays x;
+  CK(cudaMalloc(&x.a, n * 8)); CK(cudaMalloc(&x.b, n * 8)); CK(cudaMalloc(&x.c, n * 8));
+  double* d_out; CK(cudaMalloc(&d_out, 8));
+  const bool big = log2n >= 27;
+  Cfg cf[5];
+  for (int op = 0; op < 5; op++) cf[op] = baseline(op);
+  cf[OP_ADD].block = cf[OP_TRIAD].block = big ? 512 : 256;
+  cf[OP_NSTREAM].block = 256;
+  Launch L[5];
+  for (int op = 0; op < 5; op++) { L[op] = plan(cf[op], x, n, SC); if (!L[op].ok) { std::printf("plan failed\n"); return; } }
+  const int narr[5] = {2, 2, 3, 3, 4};
+  struct Var { const char* name; int alternate, keep_mode; double keep_mb; };
+  const Var vars[] = {{"forward, evict-first everywhere (round-2 default)", 0, 0, 0}, {"alternate direction, evict-first everywhere", 1, 0, 0},
+                      {"alternate, keep last 32 MB of traffic (normal)", 1, 1, 32}, {"alternate, keep last 64 MB (normal)", 1, 1, 64},
+                      {"alternate, keep last 96 MB (normal)", 1, 1, 96}, {"alternate, keep last 128 MB (normal)", 1, 1, 128},
+                      {"alternate, keep last 64 MB (loads normal, stores evict_last)", 1, 2, 64}, {"alternate, keep last 96 MB (loads normal, stores evict_last)", 1, 2, 96},
+                      {"alternate, keep stores of last 96 MB (evict_last), loads evict-first", 1, 3, 96},
+                      {"alternate, keep stores of last 192 MB (evict_last), loads evict-first", 1, 3, 192},
+                      {"forward only, keep last 96 MB (normal)", 0, 1, 96}};
+  const int order6[6] = {OP_COPY, OP_MUL, OP_ADD, OP_TRIAD, -1, OP_NSTREAM};
+  const int order1[1] = {OP_TRIAD};
+  const int* order = only_triad ? order1 : order6;
+  const int nk = only_triad ? 1 : 6;
+  const int iters = big ? 40 : 150;
+  for (const Var& v : vars) {
+    init_arrays(x, n);
+    double best[6] = {1e30, 1e30, 1e30, 1e30, 1e30, 1e30};
+    int dir = 0;
+    for (int it = 0; it < iters; it++) {
+      if (!only_triad && it % 40 == 0) { init_arrays(x, n); }
+      for (int k = 0; k < nk; k++) {
+        const int op = order[k];
+        const auto t0 = clk::now();
+        if (op >= 0) {
+          Launch l = L[op];
+          l.la.reverse = dir; l.la.keep_mode = v.keep_mode;
+          const double tile_bytes = (double)cf[op].block * cf[op].unroll * cf[op].vb * narr[op];
+          const unsigned long long keep_tiles = (unsigned long long)(v.keep_mb * 1048576.0 / tile_bytes);
+          l.la.keep_from = keep_tiles >= l.la.ntiles ? 0 : l.la.ntiles - keep_tiles;
+          l.go();
+        } else {
+          const size_t nchunks = n * 8 / 32768;
+          const size_t keep_chunks = (size_t)(v.keep_mb * 1048576.0 / 65536.0);
+          readsum_dir_kernel<<<(unsigned)nchunks, 512, 0, g_stream>>>(x.a, x.b, nchunks, dir, keep_chunks >= nchunks ? 0 : nchunks - keep_chunks, v.keep_mode ? 1 : 0, d_out);
+        }
+        cudaStreamSynchronize(g_stream);
+        const double t = std::chrono::duration<double, std::micro>(clk::now() - t0).count();
+        if (it > 2) best[k] = std::min(best[k], t);
+        if (v.alternate) dir ^= 1;
+      }
+    }
+    CK(cudaGetLastError());
+    if (only_triad) std::printf("zz 2^%d triad-only %-72s %9.2f us  %7.1f GB/s\n", log2n, v.name, best[0], 24.0 * n / best[0] / 1e3);
+    else {
+      double sum = 0; for (int k = 0; k < 6; k++) sum += best[k];
+      std::printf("zz 2^%d %-72s copy %7.2f mul %7.2f add %7.2f triad %7.2f dot* %7.2f nstream %7.2f  sum %8.2f us\n", log2n, v.name, best[0], best[1], best[2], best[3], best[4], best[5], sum);
+    }
+    std::fflush(stdout);
+  }
+  // correctness of the reversed sweep: triad on poisoned output
+  unsigned long long* d_bad; CK(cudaMalloc(&d_bad, 8));
+  init_arrays(x, n);
+  CK(cudaMemsetAsync(x.a, 0xff, n * 8, g_stream)); CK(cudaMemsetAsync(d_bad, 0, 8, g_stream));
+  Launch l = L[OP_TRIAD]; l.la.reverse = 1; l.la.keep_mode = 2; l.la.keep_from = l.la.ntiles / 2; l.go();
+  check_kernel<<<g_sms * 8, 512, 0, g_stream>>>(x.a, n, expected(OP_TRIAD), d_bad);
+  unsigned long long bad = 1; CK(cudaMemcpyAsync(&bad, d_bad, 8, cudaMemcpyDeviceToHost, g_stream)); CK(cudaStreamSynchronize(g_stream));
+  std::printf("zz reversed triad wrong elements: %llu\n", bad);
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) { std::fprintf(stderr, "usage: ew_lab b2b|seq <log2n> <op> <level> | lat | alt <log2n>\n"); return 1; }
   CK(cudaSetDevice(0));
@@ -851,6 +958,7 @@ int main(int argc, char** argv) {
   const std::string mode = argv[1];
   if (mode == "lat") { mode_lat(); return 0; }
   if (mode == "alt") { mode_alt(argc > 2 ? atoi(argv[2]) : 20); return 0; }
+  if (mode == "zz") { mode_zz(argc > 2 ? atoi(argv[2]) : 25, argc > 3 ? atoi(argv[3]) : 0); return 0; }
   if (mode == "seq6") { mode_seq6(argc > 2 ? atoi(argv[2]) : 25); return 0; }
   if (mode == "path") { const int op = argc > 3 ? op_by_name(argv[3]) : OP_TRIAD; mode_path(argc > 2 ? atoi(argv[2]) : 25, op < 0 ? OP_TRIAD : op); return 0; }
   if (argc < 5) { std::fprintf(stderr, "b2b/seq need <log2n> <op> <level>\n"); return 1; }

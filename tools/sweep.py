@@ -70,8 +70,8 @@ def configs(kernel, quick):
     vec_unroll = [(8, 1), (8, 2), (8, 4), (16, 1), (16, 2), (16, 4), (16, 8), (32, 1), (32, 2), (32, 4)]
     hints = (1, 2, 3, 4, 5)
     if kernel == "dot":
-        blocks = (256, 512, 1024)
-        grids = (-1, -2, -4, -8)
+        blocks = (128, 256, 512)
+        grids = (-1, -2, -4, -8, -16)
         variants = ("ticket", "two_pass")
     else:
         blocks = (128, 256, 512, 1024)
