@@ -50,7 +50,8 @@ static int launch_dot_typed(const DotCall& call) {
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
   args.tiles_per_block = call.tiles_per_block;
   args.sweep.reverse = call.reverse ? 1u : 0u;
-  args.sweep.keep_from = call.keep_from;
+  args.sweep.keep_from = call.keep_from >= 0xffffffffull ? ~0u : (unsigned)call.keep_from;
+  args.sweep.origin = 0; args.sweep.stride = 0;
   args.bell_flag = static_cast<unsigned long long*>(call.bell.flag); args.bell_seq = call.bell.seq;
   args.seq_counters = static_cast<unsigned long long*>(call.seq_counters);
   args.p2p.world = call.p2p_world; args.p2p.rank = call.p2p_rank; args.p2p.seq = call.p2p_seq;

@@ -129,9 +129,10 @@ enum L2Policy : int { L2_EVICT_FIRST = 0, L2_EVICT_NORMAL = 1, L2_EVICT_LAST = 2
 template <int KIND>
 __device__ __forceinline__ uint64_t l2_policy() {
   uint64_t policy;
-  if constexpr (KIND == L2_EVICT_FIRST) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
-  else if constexpr (KIND == L2_EVICT_NORMAL) asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(policy));
-  else asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(policy));
+  // not volatile: a pure value (ptxas folds it into a constant), free to be hoisted and selected between
+  if constexpr (KIND == L2_EVICT_FIRST) asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  else if constexpr (KIND == L2_EVICT_NORMAL) asm("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(policy));
+  else asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(policy));
   return policy;
 }
 template <int VB, int HINT>
@@ -150,9 +151,14 @@ __device__ __forceinline__ uint64_t make_policy() {
 //              2^25 fp64, six-kernel sequence of blocking calls: 655 us forward -> 635 us alternating -> 627 us with
 //              the last 96 MB kept; at 2^27 and beyond keeping HURTS (the kept lines take write-combining room from the
 //              stream: +2.6 % at 2^29), alternating alone still gains 0.3-0.6 %.
+// The elementwise kernels take the direction as an affine map, prepared by the launcher so that the per-block prologue
+// (the latency before a block's first load, which a one-tile-per-block grid pays 2^19 times at 2^29) stays short:
+// dispatch index p starts at vector origin + stride*p, stride = +-(vectors per tile).  p < 2^32 (checked on the host).
 struct SweepArgs {
-  unsigned long long keep_from;
-  unsigned int reverse;
+  unsigned long long origin;  // ew: first vector of dispatch tile 0 (0, or (ntiles-1)*tile_vecs when reversed)
+  long long stride;           // ew: +tile_vecs or -tile_vecs
+  unsigned int keep_from;     // dispatch index (ew: tile, dot: block) from which lines are kept; ~0u: none
+  unsigned int reverse;       // dot: logical block = gridDim.x-1-blockIdx.x
 };
 
 // READONLY: the array is not written by this kernel (-> .nc, the non-coherent path).
@@ -279,6 +285,9 @@ struct EwArgs {
   void* a;
   void* b;
   void* c;
+  char* va;                   // a + head, b + head, c + head: the VB-aligned bases of the vector part
+  char* vb;
+  char* vc;
   unsigned long long nvec;    // full vectors after head
   unsigned long long ntiles;  // ceil(nvec / (blockDim.x * UNROLL))
   unsigned long long n;       // total elements
@@ -314,14 +323,16 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
   T* const a = static_cast<T*>(args.a);
   T* const b = static_cast<T*>(args.b);
   T* const c = static_cast<T*>(args.c);
-  char* const va = reinterpret_cast<char*>(a + args.head);
-  char* const vb = reinterpret_cast<char*>(b + args.head);
-  char* const vc = reinterpret_cast<char*>(c + args.head);
+  char* const va = args.va;
+  char* const vb = args.vb;
+  char* const vc = args.vc;
 
   const unsigned long long nvec = args.nvec;
   const unsigned long long tile_vecs = (unsigned long long)blockDim.x * UNROLL;
 
   const uint64_t body_policy = make_policy<VB, HINT>();
+  uint64_t keep_ld_policy = 0, keep_st_policy = 0;
+  if constexpr (HINT == H_EVICT_FIRST) { keep_ld_policy = l2_policy<L2_EVICT_NORMAL>(); keep_st_policy = l2_policy<L2_EVICT_LAST>(); }
   Elems<T, VB> init_a, init_b, init_c;
   if constexpr (OP == OP_INIT) {
 #pragma unroll
@@ -329,12 +340,15 @@ ew_kernel(const EwArgs args, const T s0, const T s1, const T s2) {
   }
 
   for (unsigned long long ptile = blockIdx.x; ptile < args.ntiles; ptile += gridDim.x) {
-    const unsigned long long tile = args.sweep.reverse ? args.ntiles - 1 - ptile : ptile;
-    const unsigned long long v0 = tile * tile_vecs + threadIdx.x;
-    const bool full = (tile + 1) * tile_vecs <= nvec;  // block-uniform
+    const unsigned p32 = (unsigned)ptile;
+    const unsigned long long vbase = args.sweep.origin + (unsigned long long)(args.sweep.stride * (long long)p32);
+    const unsigned long long v0 = vbase + threadIdx.x;
+    const bool full = vbase + tile_vecs <= nvec;  // block-uniform
     uint64_t policy = body_policy, st_policy = body_policy;
     if constexpr (HINT == H_EVICT_FIRST) {
-      if (ptile >= args.sweep.keep_from) { policy = l2_policy<L2_EVICT_NORMAL>(); st_policy = l2_policy<L2_EVICT_LAST>(); }
+      const bool keep = p32 >= args.sweep.keep_from;
+      policy = keep ? keep_ld_policy : body_policy;
+      st_policy = keep ? keep_st_policy : body_policy;
     }
 
     Words<VB> wa[UNROLL], wb[UNROLL], wc[UNROLL];

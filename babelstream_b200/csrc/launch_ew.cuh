@@ -37,8 +37,19 @@ int launch_ew_typed(const EwCall& call) {
   EwArgs args;
   args.a = call.a; args.b = call.b; args.c = call.c;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
+  const size_t head_bytes = (size_t)call.g.head * sizeof(T);
+  args.va = static_cast<char*>(call.a) + head_bytes;
+  args.vb = static_cast<char*>(call.b) + head_bytes;
+  args.vc = static_cast<char*>(call.c) + head_bytes;
+  if (call.g.ntiles >> 32) {
+    set_error("launch shape gives %llu tiles (2^32 or more): use a larger block or unroll", (unsigned long long)call.g.ntiles);
+    return B200_EINVAL;
+  }
+  const unsigned long long tile_vecs = (unsigned long long)call.r.block * (unsigned)u;
   args.sweep.reverse = call.reverse ? 1u : 0u;
-  args.sweep.keep_from = call.keep_from;
+  args.sweep.origin = call.reverse && call.g.ntiles ? (call.g.ntiles - 1) * tile_vecs : 0;
+  args.sweep.stride = call.reverse ? -(long long)tile_vecs : (long long)tile_vecs;
+  args.sweep.keep_from = call.keep_from >= 0xffffffffull ? ~0u : (unsigned)call.keep_from;
   args.bell.ticket = static_cast<unsigned int*>(call.bell.ticket);
   args.bell.flag = static_cast<unsigned long long*>(call.bell.flag);
   args.bell.seq = call.bell.seq;

@@ -50,29 +50,46 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   r.variant = B200_VARIANT_LDST;
   r.grid_policy = INT_MAX;  // one tile per block: always beats a persistent grid-stride loop (by 4-10 %)
   // ---- the per-size table (auto) ------------------------------------------------------------------
-  // Sources: round 1 tools/sweep.py (profiles/r01/sweep_f64_top.csv: 6560 shapes, back to back) and round 2
-  // tools/lab/ew_lab (profiles/r02/lab_*.csv: blocking calls in the driver's kernel order, which is what
-  // src/main.cpp times).  Four classes by the footprint F of the three arrays against the L2 size:
+  // Sources: round 1 tools/sweep.py (profiles/r01/sweep_f64_top.csv: 6560 shapes, back to back), round 2
+  // tools/lab/ew_lab (profiles/r02/lab_*: blocking calls in the driver's kernel order, which is what src/main.cpp
+  // times) and the driver itself with BABELSTREAM_B200_TUNE overrides (profiles/r02/driver_session_*.txt).
+  // The table assumes that consecutive kernels sweep in opposite directions (B200_LAUNCH_REVERSE on every other
+  // launch: LEVEL 2's default, see SweepArgs in kernels.cuh): what a kernel touches last is what the next one
+  // reads first, so the cache policy decides how much of the 126 MB L2 that hand-over can use.
+  // Classes by the footprint F of the three arrays against the L2 size:
   //
   //   SIZE_L2     F <= 0.8 L2   launch-latency bound (8-20 us per call): fat threads in small blocks, default
   //                             cache policy so that consecutive kernels hit in L2
-  //   SIZE_KNEE   F <= 3.2 L2    part of every array still lives in L2 when the next kernel reads it: same shape,
+  //   SIZE_KNEE   F <= 3.2 L2   part of every array still lives in L2 when the next kernel reads it: same shape,
   //                             default policy (no evict-first: the lines are wanted again)
   //   SIZE_HBM    F <= 16 L2    HBM-bound, 50-250 us per call: ramp-up and tail are 3-4 % of the call, and they
   //                             shrink with the tile -- 4 KB per array per block (256 threads x 16 B) runs the
   //                             blocking call 2.3 us (triad, add) faster than 8 KB at 2^25 fp64 although both
-  //                             stream at the same 7.0 TB/s back to back
+  //                             stream at the same 7.0 TB/s back to back.
+  //                             F <= 8 L2 (2^25 fp64): evict-first for the body of the sweep, the last 128 MB of
+  //                             traffic kept (loads evict-normal, stores evict-last).  Six-kernel step, driver-timed:
+  //                             646 us forward -> 625 us alternating, 96 MB kept -> 617.6 us with 128 MB kept (one
+  //                             policy for everything: 626 us default, 635 us no-allocate).
+  //                             8 L2 < F (2^26 fp64): default policy for everything, nothing pinned: 1223 us against
+  //                             1228 us (evict-first + keep) and 1254 us forward.
   //   SIZE_HBM_XL beyond        steady state is everything: 8 KB per array per block streams 1.2-1.4 % faster at
-  //                             2^29 fp64 than 4 KB (7.21 vs 7.12 TB/s), the ~2 us of tail no longer matter
+  //                             2^29 fp64 than 4 KB, the ~2 us of tail no longer matter.  L1 no-allocate, normal L2
+  //                             priority for all lines: the step takes 2417 / 4801 / 9561 us at 2^27 / 2^28 / 2^29
+  //                             against 2428 / 4818 / 9589 us with evict-first and 2445 / 4828 / 9594 us forward;
+  //                             triad alone at 2^29: 1780-1783 us (7.23-7.24 TB/s) against 1787 us evict-first
+  //                             alternating and 1793 us forward.
   //
-  // All HBM classes: evict-first on loads AND stores.  Back to back the hints differ by < 0.5 %, but in the
-  // driver's sequence a kernel whose loads keep the default policy runs 3-4 us slower at 2^25 (its lines
-  // displace the previous kernel's dirty lines, whose write-back it then waits for).
-  // What did NOT help (profiles/r02/lab_notes.md): cp.async.bulk staging through shared memory with either
+  // Mixing priorities is what hurts at the large sizes: lines stored evict-last (or loaded evict-normal) among
+  // evict-first traffic are never displaced by it and squat in L2 for the following kernels, whose streams then
+  // thrash in what is left (add with the default policy between evict-first neighbours at 2^28: add -11 us, the
+  // triad and dot after it +18 us each; a kept tail at 2^29: triad +2.6 %).
+  // What did NOT help (profiles/r02/README.md): cp.async.bulk staging through shared memory with either
   // register or bulk stores (the cub::DeviceTransform ublkcp shape), L2 prefetch ahead of the loads (per-line
   // prefetch.global.L2 -- what the reference's thrust model runs -- or cp.async.bulk.prefetch.L2), persistent
   // multi-stage rings: all within +-0.5 % of plain LDG/STG at 2^25 and 1-2.5 % slower at 2^29.
-  r.cache_hint = cls <= SIZE_KNEE ? B200_HINT_DEFAULT : B200_HINT_EVICT_FIRST;
+  const double footprint = 3.0 * (double)n * elem_bytes / (double)l2_bytes;
+  const bool keep_tail = cls == SIZE_HBM && footprint <= 8.0;
+  r.cache_hint = cls == SIZE_HBM_XL ? B200_HINT_NOALLOC : keep_tail ? B200_HINT_EVICT_FIRST : B200_HINT_DEFAULT;
   switch (kernel) {
     case B200_COPY: case B200_MUL: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
     case B200_ADD: case B200_TRIAD:
@@ -83,26 +100,27 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
       break;
     case B200_INIT: r.vec_bytes = 32; r.unroll = 1; r.block = 256; break;
     case B200_DOT:
-      // read-only: a bounded grid-stride grid (the partials must fit the workspace).  Tuned in the
-      // driver's own situation -- blocking call, issued right after triad whose dirty lines are
+      // read-only: a bounded grid (the partials must fit the workspace), each block adding one contiguous chunk.
+      // Tuned in the driver's own situation -- blocking call, issued right after triad whose dirty lines are
       // still draining from L2 (profiles/r01/sweep_dot_blocking_after_triad_top.csv): 8 blocks of 512
       // threads per SM (two waves, the second balancing the first) with 2 x 16-byte loads per
       // operand in flight is within 1.1 % of the best shape at 2^25, 2^27 and 2^29; shapes with
-      // less than full occupancy win in isolation but lose up to 10 % in sequence.
+      // less than full occupancy win in isolation but lose up to 10 % in sequence.  Same cache policy as the
+      // elementwise kernels of the class (profiles/r02/driver_session_g_hints.txt: a dot that does not allocate
+      // among default-policy neighbours is 4 us faster at 2^26 and makes the nstream after it 4.5 us slower).
       r.variant = B200_VARIANT_DOT_TICKET;
       r.vec_bytes = 16; r.unroll = 2; r.block = 512; r.grid_policy = -8;
-      // evict-first where the end of the sweep is kept for the next kernel (SIZE_HBM), else L1 no-allocate only
-      r.cache_hint = l2_resident ? B200_HINT_DEFAULT : cls == SIZE_HBM ? B200_HINT_EVICT_FIRST : B200_HINT_NOALLOC;
       break;
   }
-  // The last 96 MB of a sweep stay in L2 for the next kernel -- only where that pays (see SweepArgs in kernels.cuh)
-  r.keep_mb = (cls == SIZE_HBM && r.cache_hint == B200_HINT_EVICT_FIRST) ? 96 : 0;
+  // The tail of a sweep stays in L2 for the next kernel -- only where that pays (see SweepArgs in kernels.cuh)
+  r.keep_mb = keep_tail ? 128 : 0;
   if (cls <= SIZE_KNEE) {
     // Working set inside L2 (<= 2^22 doubles) or not much larger (2^23, 2^24): one 32-byte access per thread in
     // 256-thread blocks.  Driver-timed candidates: profiles/r01/small_size_candidates.txt (2^20..2^22),
     // profiles/r02/class_calibration.txt (2^20..2^24: at the knee the six-kernel step takes 181.6 us with this
     // shape and default policy against 189.6 us with the HBM shapes + no-allocate and 229.6 us for cuda-stream
-    // at 2^23; dot alone 28.3 vs 33.5 us because triad's output stays in L2 for it).
+    // at 2^23; dot alone 28.3 vs 33.5 us because triad's output stays in L2 for it).  The alternating sweep takes
+    // the knee further: 176.7 us at 2^23 and 330.2 us at 2^24 against 185.3 / 350.9 us forward.
     if (kernel == B200_DOT) { if (l2_resident) { r.vec_bytes = 32; r.unroll = 4; r.block = 256; r.grid_policy = -2; } }
     else { r.vec_bytes = 32; r.unroll = 1; r.block = 256; }
   }

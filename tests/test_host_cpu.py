@@ -119,8 +119,11 @@ def test_resolve_cfg_size_classes():
         shapes[log2n] = (t.vec_bytes, t.unroll, t.block, t.cache_hint)
     assert shapes[20] == shapes[22] and shapes[20][3] == bs.HINTS["default"], "L2-resident: default cache policy"
     assert shapes[23][3] == bs.HINTS["default"] and shapes[24][3] == bs.HINTS["default"], "knee: keep the lines in L2"
-    assert shapes[25] == shapes[26] and shapes[27] == shapes[29], "the tile grows between 2^26 and 2^27 (fp64)"
-    assert shapes[25][3] == bs.HINTS["evict_first"] and shapes[29][3] == bs.HINTS["evict_first"], "HBM-bound: evict-first"
+    assert shapes[25][:3] == shapes[26][:3] and shapes[27] == shapes[29], "the tile grows between 2^26 and 2^27 (fp64)"
+    assert shapes[25][3] == bs.HINTS["evict_first"], "a few times L2: evict-first body, the tail of the sweep kept"
+    assert shapes[26][3] == bs.HINTS["default"] and shapes[29][3] == bs.HINTS["noalloc"], "larger: one L2 priority for all lines"
+    keep = {k: bs.resolve_cfg("add", 1 << k, 8, num_sms=148, l2_bytes=l2)[0].keep_mb for k in (22, 24, 25, 26, 29)}
+    assert keep == {22: 0, 24: 0, 25: 128, 26: 0, 29: 0}, "only the evict-first class pins the end of a sweep"
     tile = lambda s: s[0] * s[1] * s[2]
     assert tile(shapes[25]) < tile(shapes[29]), "short HBM-bound calls run smaller tiles (ramp-up and tail) than 2^29"
     # the class depends on BYTES, not elements: fp32 at 2n is the same class as fp64 at n

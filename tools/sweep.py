@@ -122,6 +122,9 @@ def main():
     ap.add_argument("--blocking", action="store_true", help="time launch+wait per call with the host clock (min), like the driver")
     ap.add_argument("--budget-s", type=float, default=1e9)
     ap.add_argument("--after", default="", help="with --blocking: run this kernel (default config) before every timed call")
+    ap.add_argument("--alternate", action="store_true", help="consecutive launches sweep in opposite directions (B200_LAUNCH_REVERSE)")
+    ap.add_argument("--hints", default="", help="comma-separated cache hints to try (default: all)")
+    ap.add_argument("--top", type=int, default=0, help="write only the best N rows per kernel and size")
     args = ap.parse_args()
 
     if args.pad_test:
@@ -145,14 +148,22 @@ def main():
             base = "copy" if kernel == "copy_async" else kernel
             nbytes = bs.WEIGHTS[base] * n * eb
             best = []
+            first_row = len(rows)
             for kw in configs(kernel, args.quick):
                 if time.time() - t_start > args.budget_s:
                     break
-                cfg = bs.LaunchCfg.make(**kw)
+                if args.hints and str(kw.get("cache_hint")) not in args.hints.split(","):
+                    continue
+                pair = [bs.LaunchCfg.make(**kw), bs.LaunchCfg.make(flags=bs.LAUNCH_REVERSE if args.alternate else 0, **kw)]
+                turn = [0]
+
+                def next_cfg(pair=pair, turn=turn):
+                    turn[0] ^= 1
+                    return pair[turn[0]]
                 if base == "dot":
-                    fn = lambda: bs.launch_dot(a.data_ptr(), b.data_ptr(), n, eb, ws.data_ptr(), out.data_ptr(), cfg=cfg, stream=st)
+                    fn = lambda: bs.launch_dot(a.data_ptr(), b.data_ptr(), n, eb, ws.data_ptr(), out.data_ptr(), cfg=next_cfg(), stream=st)
                 else:
-                    fn = lambda: bs.launch(base, a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, cfg=cfg, stream=st)
+                    fn = lambda: bs.launch(base, a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, cfg=next_cfg(), stream=st)
                 try:
                     before = (lambda: bs.launch(args.after, a.data_ptr(), b.data_ptr(), c.data_ptr(), n, eb, stream=st)) if args.after else None
                     ms = time_blocking(fn, max(reps, 20), before=before) if args.blocking else time_launch(fn, reps)
@@ -160,7 +171,7 @@ def main():
                     print("skip", kernel, kw, e)
                     continue
                 gbs = nbytes / ms / 1e6
-                row = dict(kernel=kernel, dtype=args.dtype, log2n=log2n, mode="blocking" if args.blocking else "back_to_back", ms=round(ms, 6), gbs=round(gbs, 1), reps=reps,
+                row = dict(kernel=kernel, dtype=args.dtype, log2n=log2n, mode=("blocking" if args.blocking else "back_to_back") + ("_alternate" if args.alternate else ""), ms=round(ms, 6), gbs=round(gbs, 1), reps=reps,
                            l2_note="arrays>L2" if 3 * n * eb > 2 * (126 << 20) else "L2-resident", **{k: kw.get(k, "") for k in
                            ("vec_bytes", "unroll", "block", "grid", "cache_hint", "variant", "stages", "chunk_bytes")})
                 rows.append(row)
@@ -168,6 +179,8 @@ def main():
                 if base in ("triad", "nstream", "add", "mul"):
                     # keep the values bounded over thousands of launches
                     a.fill_(0.1); b.fill_(0.2); c.zero_()
+            if args.top:
+                rows[first_row:] = sorted(rows[first_row:], key=lambda r: -r["gbs"])[:args.top]
             best.sort(key=lambda t: -t[0])
             print(f"== {kernel} {args.dtype} 2^{log2n}: {len(best)} configs, top 8:")
             for gbs, kw in best[:8]:
