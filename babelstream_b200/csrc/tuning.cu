@@ -91,7 +91,10 @@ int resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
   const bool keep_tail = cls == SIZE_HBM && footprint <= 8.0;
   r.cache_hint = cls == SIZE_HBM_XL ? B200_HINT_NOALLOC : keep_tail ? B200_HINT_EVICT_FIRST : B200_HINT_DEFAULT;
   switch (kernel) {
-    case B200_COPY: case B200_MUL: r.vec_bytes = 16; r.unroll = 2; r.block = 512; break;
+    case B200_COPY: case B200_MUL:
+      // one read and one write stream: two 1024-thread blocks per SM run the alternating blocking call 0.7 % faster
+      // at 2^28 than four of 512 (612 vs 617 us; profiles/r02/sweep_alt_2p28_top.csv), no difference at 2^25
+      r.vec_bytes = 16; r.unroll = 2; r.block = cls == SIZE_HBM_XL ? 1024 : 512; break;
     case B200_ADD: case B200_TRIAD:
       r.vec_bytes = 16; r.unroll = 1; r.block = cls == SIZE_HBM_XL ? 512 : 256; break;
     case B200_NSTREAM:

@@ -6,7 +6,7 @@ G=${1:-2}
 O=gpurun_out/r2m$G
 mkdir -p $O
 nvidia-smi -L | head -8
-timeout 900 python -m pytest tests -m gpu -q -k "multi or group or combine or timeout" > $O/pytest_multi_${G}gpu.log 2>&1; echo "pytest multi rc=$?"; tail -6 $O/pytest_multi_${G}gpu.log
+timeout 1500 python -m pytest tests -m gpu -q -rs > $O/pytest_gpu_${G}gpu.log 2>&1; echo "pytest rc=$?"; tail -8 $O/pytest_gpu_${G}gpu.log
 run_bench() { # N extra-args
   local N=$1; shift
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 295$N bench.py --gpus $N --steps 100 --warmup 5 "$@" > $O/bench_$N.json 2> $O/bench_$N.err
