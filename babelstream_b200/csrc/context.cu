@@ -3,9 +3,10 @@
 // Three device-resident arrays of n elements, sharded contiguously over G GPUs of one box
 // (b200_shard_range).  Every public call is blocking, as src/Stream.h:36 demands.
 //   G == 1 : the caller's thread launches and waits; no helper threads at all.
-//   G  > 1 : one worker thread per GPU, released by a shared sequence number and joined through ONE
-//            completion counter, so that the G launches start together instead of one after another
-//            from a single thread (SURVEY.md section 7 "launch skew").
+//   G  > 1 : the caller's thread drives GPU 0 itself and G-1 worker threads drive the others, released by a
+//            shared sequence number and joined through ONE completion counter, so that the G launches start
+//            together instead of one after another from a single thread (SURVEY.md section 7 "launch skew").
+//            Each worker is pinned to its own core among the CPUs local to its GPU (option pin=off: not).
 // Every kernel call replays a one-node CUDA graph that was captured the first time the call was made
 // with these arguments (a "plan"): the arrays, the shape and the scalar never change between the calls
 // of a benchmark run, and cudaGraphLaunch + cudaStreamSynchronize returns 2.0-2.5 us sooner than
@@ -15,7 +16,9 @@
 // shard to one T, and the G values are combined inside the dot kernel by peer stores over NVLink
 // (dot_combine=p2p, the default when every GPU pair has peer access), by ONE ncclAllReduce of
 // count 1 (nccl) or by a rank-order sum of G mapped host scalars (host).
+#include <ctype.h>
 #include <dlfcn.h>
+#include <sched.h>
 #include <nccl.h>  // types only: the library is dlopen'ed, so single-GPU use needs no NCCL at all
 
 #include <atomic>
@@ -82,6 +85,7 @@ enum { SYNC_AUTO = -1, SYNC_STREAM = 0, SYNC_SPIN = 1, SYNC_DOORBELL = 2 };
 
 struct Shard {
   int dev = 0;
+  int pin_cpu = -1;              // CPU the shard's worker thread is pinned to (-1: unpinned)
   size_t begin = 0, count = 0;
   cudaStream_t stream = nullptr;
   void *a = nullptr, *b = nullptr, *c = nullptr;
@@ -137,6 +141,7 @@ struct b200_ctx {
   int sync_mode = SYNC_AUTO;
   int caller_device = -1;    // the device that was current when b200_create was called; restored by create and destroy
   bool use_graphs = true;    // option launch=graph|direct
+  bool pin = true;           // option pin=auto|off: pin every worker thread to a core of its own near its GPU
   bool alternate = true;     // option sweep=alternate|forward: consecutive kernels sweep in opposite directions
   int next_reverse = 0;      // direction of the next kernel call
   uint64_t tune_gen = 1;     // bumped by every option change: invalidates the cached plans
@@ -302,13 +307,13 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
   using clk = std::chrono::steady_clock;
   clk::time_point t0, t1, t2;
   if (ctx->hostprof) t0 = clk::now();
-  // G == 1 runs on the caller's thread: make the shard's device current for the call and hand the caller's
-  // device back afterwards (the workers of G > 1 own their device for life)
+  // Shard 0 runs on the caller's thread: make the shard's device current for the call and hand the caller's
+  // device back afterwards (the workers of shards 1..G-1 own their device for life)
   struct DeviceScope {
     int saved = -1, mine = -1;
     ~DeviceScope() { if (saved >= 0 && saved != mine) cudaSetDevice(saved); }
   } scope;
-  if (ctx->ngpus == 1) {
+  if (g == 0) {
     scope.mine = s->dev;
     if (cudaGetDevice(&scope.saved) != cudaSuccess) { (void)cudaGetLastError(); scope.saved = -1; }
     if (scope.saved != s->dev) B200_CUDA(cudaSetDevice(s->dev));
@@ -409,9 +414,91 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
   return B200_OK;
 }
 
+// One CPU per worker thread: among the CPUs this process may run on, prefer those local to the worker's GPU
+// (/sys/bus/pci/devices/<bdf>/local_cpulist) and a physical core no other worker -- and not the caller, who
+// drives GPU 0 from whatever core it is on -- has been given.  Workers spin between the calls of a
+// benchmark run; two of them on the hyper-threads of one core, or one migrating in the middle of a call,
+// shows up directly in the join time.  Anything unreadable: the shard stays unpinned.
+static std::vector<int> parse_cpulist(const char* path) {
+  std::vector<int> cpus;
+  FILE* f = fopen(path, "r");
+  if (!f) return cpus;
+  char buf[4096];
+  if (fgets(buf, sizeof buf, f)) {
+    for (char* p = buf; *p && *p != '\n';) {
+      char* end;
+      const long lo = strtol(p, &end, 10);
+      if (end == p) break;
+      long hi = lo;
+      p = end;
+      if (*p == '-') { hi = strtol(p + 1, &end, 10); p = end; }
+      for (long c = lo; c <= hi && c < CPU_SETSIZE; c++) cpus.push_back((int)c);
+      if (*p == ',') p++;
+    }
+  }
+  fclose(f);
+  return cpus;
+}
+
+static long core_key(int cpu) {
+  char path[128];
+  long pkg = 0, core = cpu;
+  snprintf(path, sizeof path, "/sys/devices/system/cpu/cpu%d/topology/physical_package_id", cpu);
+  if (FILE* f = fopen(path, "r")) { if (fscanf(f, "%ld", &pkg) != 1) pkg = 0; fclose(f); }
+  snprintf(path, sizeof path, "/sys/devices/system/cpu/cpu%d/topology/core_id", cpu);
+  if (FILE* f = fopen(path, "r")) { if (fscanf(f, "%ld", &core) != 1) core = cpu; fclose(f); }
+  return pkg * 100000 + core;
+}
+
+static void choose_worker_cpus(b200_ctx* ctx) {
+  cpu_set_t allowed;
+  CPU_ZERO(&allowed);
+  if (sched_getaffinity(0, sizeof allowed, &allowed) != 0) return;
+  if (CPU_COUNT(&allowed) < ctx->ngpus) return;  // fewer CPUs than threads: pinning would only stack them
+  std::vector<long> used_cores;
+  std::vector<int> used_cpus;
+  const int here = sched_getcpu();
+  if (here >= 0) { used_cores.push_back(core_key(here)); used_cpus.push_back(here); }
+  auto is_in = [](const auto& v, auto x) { for (auto y : v) if (y == x) return true; return false; };
+  for (int g = 1; g < ctx->ngpus; g++) {
+    Shard* s = ctx->shards[g];
+    std::vector<int> local;
+    char bdf[32] = {0};
+    if (cudaDeviceGetPCIBusId(bdf, sizeof bdf, s->dev) == cudaSuccess) {
+      for (char* p = bdf; *p; p++) *p = (char)tolower(*p);
+      char path[128];
+      snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/local_cpulist", bdf);
+      local = parse_cpulist(path);
+    } else {
+      (void)cudaGetLastError();
+    }
+    std::vector<int> everywhere;
+    for (int c = 0; c < CPU_SETSIZE; c++) if (CPU_ISSET(c, &allowed)) everywhere.push_back(c);
+    int pick = -1;
+    // 1. local CPU on an untouched core  2. any CPU on an untouched core  3. a local, then any, untouched hyper-thread
+    for (int pass = 0; pass < 4 && pick < 0; pass++) {
+      const std::vector<int>& pool = (pass == 0 || pass == 2) ? local : everywhere;
+      for (int c : pool) {
+        if (!CPU_ISSET(c, &allowed) || is_in(used_cpus, c)) continue;
+        if (pass < 2 && is_in(used_cores, core_key(c))) continue;
+        pick = c;
+        break;
+      }
+    }
+    s->pin_cpu = pick;
+    if (pick >= 0) { used_cpus.push_back(pick); used_cores.push_back(core_key(pick)); }
+  }
+}
+
 static void worker_main(b200_ctx* ctx, int g) {
   Shard* s = ctx->shards[g];
   cudaSetDevice(s->dev);
+  if (s->pin_cpu >= 0) {
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    CPU_SET(s->pin_cpu, &set);
+    if (sched_setaffinity(0, sizeof set, &set) != 0) s->pin_cpu = -1;  // not allowed here: run unpinned
+  }
   uint64_t seen = 0;
   for (;;) {
     // spin briefly (the benchmark issues calls back to back), then sleep on the condition variable
@@ -442,8 +529,12 @@ static int run_all(b200_ctx* ctx, const Command& cmd) {
     { std::lock_guard<std::mutex> lock(ctx->mu); }
     ctx->cv.notify_all();
   }
+  // GPU 0 is driven from here: no hand-over on the path of the shard whose result the caller reads
+  Shard* s0 = ctx->shards[0];
+  s0->status = shard_execute(ctx, 0, cmd);
+  if (s0->status != B200_OK) s0->error = b200_last_error();
   // join: ONE counter that every worker bumps once per command (not G flags polled in series)
-  const uint64_t all_done = target * (uint64_t)ctx->ngpus;
+  const uint64_t all_done = target * (uint64_t)(ctx->ngpus - 1);
   unsigned spins = 0;
   while (ctx->done_total.load(std::memory_order_acquire) < all_done) {
     if (++spins < (1u << 22)) B200_PAUSE();
@@ -487,6 +578,10 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
     if (val != "alternate" && val != "forward") { set_error("sweep must be alternate or forward, got '%s'", val.c_str()); return B200_EINVAL; }
     ctx->alternate = val == "alternate";
     ctx->next_reverse = 0;
+  } else if (key == "pin") {
+    if (val != "auto" && val != "off") { set_error("pin must be auto or off, got '%s'", val.c_str()); return B200_EINVAL; }
+    if (ctx->created) { set_error("pin is fixed when the worker threads start: pass it to b200_create_opts or set BABELSTREAM_B200_PIN"); return B200_EINVAL; }
+    ctx->pin = val == "auto";
   } else if (key == "launch") {
     if (val != "graph" && val != "direct") { set_error("launch must be graph or direct, got '%s'", val.c_str()); return B200_EINVAL; }
     ctx->use_graphs = val == "graph";
@@ -703,7 +798,7 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
   if (cudaGetDevice(&ctx->caller_device) != cudaSuccess) { (void)cudaGetLastError(); ctx->caller_device = -1; }
 
   // options from the environment: BABELSTREAM_B200_<KEY>
-  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem", "launch", "sweep"};
+  const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem", "launch", "sweep", "pin"};
   for (const char* k : keys) {
     std::string env = "BABELSTREAM_B200_";
     for (const char* p = k; *p; p++) env += (char)toupper(*p);
@@ -815,7 +910,8 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
   if (ngpus > 1) {
     rc = ensure_combine_ready(ctx);
     if (rc) return fail(rc);
-    for (int g = 0; g < ngpus; g++) ctx->workers.emplace_back(worker_main, ctx, g);
+    if (ctx->pin) choose_worker_cpus(ctx);
+    for (int g = 1; g < ngpus; g++) ctx->workers.emplace_back(worker_main, ctx, g);
   }
   cudaSetDevice(ctx->caller_device >= 0 ? ctx->caller_device : first_device);  // the caller's current device is left as it was
   ctx->created = true;
@@ -907,6 +1003,15 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
                         : "  sweep: forward (always bottom-up)\n";
   out += ctx->use_graphs ? "  launch: every call replays a captured one-kernel CUDA graph (launch=direct: <<<>>>)\n"
                          : "  launch: direct (<<<>>> per call)\n";
+  if (ctx->ngpus > 1) {
+    out += "  threads: the caller drives GPU 0; workers";
+    for (int g = 1; g < ctx->ngpus; g++) {
+      if (ctx->shards[g]->pin_cpu >= 0) snprintf(line, sizeof line, " %d->cpu%d", g, ctx->shards[g]->pin_cpu);
+      else snprintf(line, sizeof line, " %d->unpinned", g);
+      out += line;
+    }
+    out += "\n";
+  }
   snprintf(buf, (size_t)buflen, "%s", out.c_str());
   return B200_OK;
 }

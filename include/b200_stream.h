@@ -255,6 +255,8 @@ int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes);
  * cudaGraphLaunch + wait returns 2.0-2.5 us sooner than <<<>>> + wait on B200),
  * sweep=alternate|forward (alternate, the default: consecutive kernel calls sweep the arrays in opposite directions,
  * see B200_LAUNCH_REVERSE),
+ * pin=auto|off (create time only, ngpus > 1: the caller's thread drives GPU 0, one worker thread drives each other
+ * GPU; auto, the default, pins every worker to a core of its own among the CPUs local to its GPU),
  * tune=<kernel>:<field>=<v>,...;...   (fields: vec unroll block grid hint stages chunk keep flags) */
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
 int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */
