@@ -14,8 +14,9 @@
 // sequence numbers live in device memory for the same reason.
 // The elementwise kernels never communicate.  dot is the one exchange step: each GPU reduces its
 // shard to one T, and the G values are combined inside the dot kernel by peer stores over NVLink
-// (dot_combine=p2p, the default when every GPU pair has peer access), by ONE ncclAllReduce of
-// count 1 (nccl) or by a rank-order sum of G mapped host scalars (host).
+// by a rank-order sum of G mapped host scalars whose doorbells the caller polls (dot_combine=host, the
+// default inside one process), inside the dot kernel by peer stores over NVLink (p2p: what process groups
+// use, b200_join_group) or by ONE ncclAllReduce of count 1 (nccl).
 #include <ctype.h>
 #include <dlfcn.h>
 #include <sched.h>
@@ -96,6 +97,7 @@ struct Shard {
   void* dot_host_dev = nullptr;  // device-side alias of dot_host
   void* bell_ticket = nullptr;   // device word of the elementwise kernels' doorbell
   unsigned long long bell_seq = 0;      // last value the elementwise doorbell was asked to ring with
+  unsigned long long dot_deferred = 0;  // dot_combine=host: doorbell value the CALLER still has to wait for (0: none)
   void* seq_counters = nullptr;  // device, 2 x 8 bytes: dot's doorbell value and all-reduce sequence number (bumped by the kernel)
   unsigned long long dot_bell_seq = 0;  // host mirror of seq_counters[0]
   struct Plan {                  // one captured launch, replayed while its key matches
@@ -364,7 +366,11 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
     if (ctx->timing) B200_CUDA(cudaEventRecord(s->ev1, s->stream));
     // In-process fused all-reduce: every GPU ends up with the same bits and the caller reads GPU 0's copy, so
     // only worker 0 has to see the kernel finish; stream order protects whatever the others enqueue next.
-    const bool skip_wait = is_dot && g != 0 && ctx->ngpus > 1 && ctx->combine == COMBINE_P2P && !ctx->timing;
+    // dot_combine=host: the caller polls every GPU's doorbell itself (b200_dot), so a worker's own wake-up and the
+    // join are not on the path of the last partial to arrive either.
+    const bool host_defer = is_dot && g != 0 && ctx->ngpus > 1 && ctx->combine == COMBINE_HOST && bell && !ctx->timing;
+    s->dot_deferred = host_defer ? want : 0;
+    const bool skip_wait = host_defer || (is_dot && g != 0 && ctx->ngpus > 1 && ctx->combine == COMBINE_P2P && !ctx->timing);
     if (!skip_wait) {
       if (int rc = bell ? bell_wait(s, want, flag_off) : stream_wait(ctx, s)) return rc;
     }
@@ -669,24 +675,22 @@ static int ensure_host_mirrors(b200_ctx* ctx) {
 
 // Bring up whatever the selected multi-GPU dot combine needs.  Caller's thread, workers idle.
 static int ensure_combine_ready(b200_ctx* ctx) {
-  if (ctx->ngpus == 1 || ctx->combine == COMBINE_HOST) return B200_OK;
+  if (ctx->ngpus == 1) return B200_OK;
   struct DeviceScope {  // the caller's current device is put back on every way out
     int saved = -1;
     DeviceScope() { if (cudaGetDevice(&saved) != cudaSuccess) { (void)cudaGetLastError(); saved = -1; } }
     ~DeviceScope() { if (saved >= 0) cudaSetDevice(saved); }
   } scope;
   if (ctx->combine == COMBINE_AUTO) {
-    // Default: the fused peer-memory all-reduce (one launch, no NCCL bring-up) whenever every pair of
-    // GPUs has peer access -- always true on an NVSwitch box -- otherwise one ncclAllReduce.
-    bool all_peers = ctx->ngpus <= kMaxPeers;
-    for (Shard* s : ctx->shards)
-      for (Shard* peer : ctx->shards) {
-        int can = 0;
-        if (s != peer && (cudaDeviceCanAccessPeer(&can, s->dev, peer->dev) != cudaSuccess || !can)) all_peers = false;
-      }
-    (void)cudaGetLastError();
-    ctx->combine = all_peers ? COMBINE_P2P : COMBINE_NCCL;
+    // Default inside ONE process: the caller is the only consumer of the sum, so every GPU stores its partial
+    // into mapped host memory and rings a doorbell there; the caller polls the G doorbells and adds the G values
+    // in rank order.  8 GPUs x 2^25 fp64, blocking dot through the driver: 49.3 TB/s (0.97 of 8 x one GPU)
+    // against 48.2 TB/s for the fused peer-memory all-reduce (whose result makes one more hop: peers -> GPU 0 ->
+    // host) and 38.0 TB/s for ncclAllReduce (profiles/r02/inprocess_8gpu.txt).  The fused all-reduce is what
+    // process groups use (b200_join_group), where every rank needs the sum.
+    ctx->combine = COMBINE_HOST;
   }
+  if (ctx->combine == COMBINE_HOST) return B200_OK;
   if (ctx->combine == COMBINE_NCCL) {
     if (ctx->nccl_ready) return B200_OK;
     if (int rc = ctx->nccl.load()) return rc;
@@ -1047,6 +1051,12 @@ int b200_dot(b200_ctx* ctx, double* result) {
   if (int rc = run_kernel(ctx, B200_DOT, 0, 0, 0)) return rc;
   double total;
   if (ctx->ngpus > 1 && ctx->combine == COMBINE_HOST) {
+    for (Shard* s : ctx->shards) {
+      if (!s->dot_deferred) continue;
+      const int rc = bell_wait(s, s->dot_deferred, 8);
+      s->dot_deferred = 0;
+      if (rc) return rc;
+    }
     // G values, added in rank order in type T: deterministic
     if (ctx->elem_bytes == 8) { double t = 0; for (Shard* s : ctx->shards) t += *static_cast<volatile double*>(s->dot_host); total = t; }
     else { float t = 0; for (Shard* s : ctx->shards) t += *static_cast<volatile float*>(s->dot_host); total = t; }

@@ -240,8 +240,9 @@ int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes);
 /* "key=value" tuning / behaviour options, also read from the environment at create time as
  * BABELSTREAM_B200_<KEY>.  Keys: contract=fast|off, copy_variant=auto|ldst|bulk|tma,
  * dot_variant=auto|two_pass|ticket, dot_combine=auto|p2p|nccl|host (multi-GPU dot: fused peer-memory
- * all-reduce inside the dot kernel | one ncclAllReduce | rank-order sum on the host; auto = p2p when
- * every pair of GPUs has peer access, else nccl), timing=0|1,
+ * all-reduce inside the dot kernel | one ncclAllReduce | rank-order sum on the host; auto = host: inside one
+ * process the caller is the only consumer of the sum and polls the G doorbells itself -- process groups joined with
+ * b200_join_group always use the fused all-reduce), timing=0|1,
  * sync=auto|stream|spin|doorbell (how a blocking call waits: cudaStreamSynchronize | cudaStreamQuery loop |
  * the kernel rings a host flag, see b200_doorbell; auto = doorbell for dot, cudaStreamSynchronize for the rest),
  * mem=device|managed|pagefault (allocation time only: b200_create_opts or the environment; managed = the reference's

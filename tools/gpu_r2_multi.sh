@@ -30,4 +30,8 @@ for rep in 1 2; do
 done
 BABELSTREAM_B200_NGPUS=1 timeout 200 ./build/b200-stream --csv --gigabytes -s 33554432 --only All 2>&1 | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,5 | tr '\n' ' ' | sed 's/^/1 GPU: /' | tee -a $O/inprocess.txt; echo
 BABELSTREAM_B200_NGPUS=$G BABELSTREAM_B200_LAUNCH=direct timeout 200 ./build/b200-stream --csv --gigabytes -s $((33554432*G)) --only All 2>&1 | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,5 | tr '\n' ' ' | sed 's/^/launch=direct: /' | tee -a $O/inprocess.txt; echo
+for opt in "BABELSTREAM_B200_DOT_COMBINE=host" "BABELSTREAM_B200_DOT_COMBINE=nccl" "BABELSTREAM_B200_PIN=off"; do
+  env $opt BABELSTREAM_B200_NGPUS=$G timeout 200 ./build/b200-stream --csv --gigabytes -s $((33554432*G)) --only All 2>&1 | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,5 | tr '\n' ' ' | sed "s/^/$opt: /" | tee -a $O/inprocess.txt; echo | tee -a $O/inprocess.txt
+done
+BABELSTREAM_B200_NGPUS=$G timeout 100 ./build/b200-stream -s $((33554432*G)) --only Triad -n 5 2>&1 | head -30 > $O/banner_${G}gpu.txt; grep -E "threads|combine" $O/banner_${G}gpu.txt
 echo "gpu_r2_multi $G done"
