@@ -161,13 +161,23 @@ def parse_stream_csv(text: str):
     return out
 
 
+# CPUs this program may use, taken before any OpenMP runtime is loaded: libgomp binds the thread that loads it
+# (OMP_PROC_BIND) and a child process would inherit that one-CPU mask.
+_START_AFFINITY = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+
+
+def _restore_affinity():
+    if _START_AFFINITY:
+        os.sched_setaffinity(0, _START_AFFINITY)
+
+
 def run_stream_binary(path, n, num_times, only="All", env=None, timeout=900, want_wall=False):
     """Runs a BabelStream binary (ours or a reference model); a non-zero exit (check_solution failed) raises."""
     e = dict(os.environ)
     e.update(env or {})
     t0 = time.perf_counter()
     p = subprocess.run([path, "--csv", "--gigabytes", "-s", str(n), "-n", str(num_times), "--only", only],
-                       capture_output=True, text=True, timeout=timeout, env=e)
+                       capture_output=True, text=True, timeout=timeout, env=e, preexec_fn=_restore_affinity)
     wall = time.perf_counter() - t0
     if p.returncode != 0:
         raise RuntimeError(f"{os.path.basename(path)} exited {p.returncode}: {p.stderr[-400:]}")
@@ -726,6 +736,9 @@ def main():
                         w["reference_omp_stream"] = whole_run(omp_bin, n, 100, env=env)
                     line["e2e_whole_run"] = w
                     extras["b200_stream_driver"] = {k: round(v["gbs"], 1) for k, v in run_stream_binary(b200_bin, n, 100).items()}
+                    extras["b200_stream_driver_sweep_forward"] = {
+                        k: round(v["gbs"], 1)
+                        for k, v in run_stream_binary(b200_bin, n, 100, env={"BABELSTREAM_B200_SWEEP": "forward"}).items()}
                 if os.path.exists(cuda_bin):
                     extras["reference_cuda_stream_driver"] = {k: round(v["gbs"], 1) for k, v in run_stream_binary(cuda_bin, n, 100).items()}
                 if os.path.exists(thrust_bin):
@@ -741,6 +754,12 @@ def main():
                           "frac_of_measured_peak": round(r["triad"]["gbs"] / peak, 4),
                           "frac_of_nominal_8000": round(r["triad"]["gbs"] / 8000, 4),
                           "frac_of_device_formula_peak": round(r["triad"]["gbs"] / device_peak, 4) if device_peak else None}
+                    # the same with every sweep bottom-up: how much of the figure is the previous call's tail still in L2
+                    rf = run_stream_binary(b200_bin, big, 30, only="Triad", env={"BABELSTREAM_B200_SWEEP": "forward"})
+                    ns["b200_stream_driver_gbs_sweep_forward"] = round(rf["triad"]["gbs"], 1)
+                    ns["sweep"] = ("default: consecutive calls sweep the arrays in opposite directions, so a call starts on the "
+                                   "<= 126 MB its predecessor left in L2 (of 12.9 GB moved per call at this size); "
+                                   "sweep_forward: every call bottom-up, as the reference's kernels run")
                     if os.path.exists(cuda_bin):
                         r2 = run_stream_binary(cuda_bin, big, 30, only="Triad")
                         ns["reference_cuda_stream_driver_gbs"] = round(r2["triad"]["gbs"], 1)
