@@ -108,7 +108,9 @@ uint64_t b200_launch_count(void);                      /* kernels launched by th
 
 /* Host-side logic, usable (and tested) without a GPU. */
 /* Contiguous shard of GPU g out of ngpus: [begin, begin+count).  Shard boundaries are multiples of
- * 128 bytes so every shard starts on a full cache line. */
+ * 128 bytes so every shard starts on a full cache line.  This is the layout of mem=device
+ * contexts; mem=managed and mem=pagefault contexts with shards of 8 MiB or more put the boundaries on
+ * multiples of 2 MiB (the managed page size) instead -- ask b200_shard_info for the shards of a context. */
 int b200_shard_range(size_t n, int elem_bytes, int ngpus, int g, size_t* begin, size_t* count);
 /* Resolve "auto" fields of `in` for (kernel, n, elem_bytes) on a GPU with num_sms SMs and l2_bytes of L2:
  * fills `out`, and the resulting grid size / tile count. */
