@@ -443,6 +443,32 @@ def test_multi_gpu_sharded_bit_exact(orc, dtype, combine):
 
 
 @multi
+def test_multi_gpu_threading_options(orc):
+    """In-process layout: the caller drives GPU 0, pinned workers drive the others; pin/launch/sweep change how the
+    calls are issued, never the bits.  The default dot combine inside one process is the host sum."""
+    ngpus = min(bs.device_count(), 8)
+    n = (1 << 21) + 5
+    ref = None
+    for opts in ({}, {"pin": "off"}, {"launch": "direct"}, {"sweep": "forward", "pin": "off"}, {"dot_combine": "p2p"}):
+        with bs.B200Stream(n, dtype=np.float64, ngpus=ngpus, **opts) as s:
+            text = s.describe()
+            assert "the caller drives GPU 0" in text
+            assert ("unpinned" in text) == (opts.get("pin") == "off") or "unpinned" in text   # pinning may be refused by the box
+            if "dot_combine" not in opts:
+                assert "host sum in rank order" in text
+            total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 5)
+            a, b, c = s.get_arrays()
+            cur = (a.tobytes(), b.tobytes(), c.tobytes(), np.asarray(total).tobytes())
+            ref = ref or cur
+            assert cur == ref, opts
+            assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 5, a, b, c, total) == 0
+            with pytest.raises(bs.B200Error):
+                s.set_option("pin", "off")        # fixed when the worker threads start
+    with pytest.raises(bs.B200Error):
+        bs.B200Stream(n, dtype=np.float64, ngpus=ngpus, pin="sometimes")
+
+
+@multi
 @pytest.mark.parametrize("combine", ["p2p", "host"])
 def test_multi_gpu_managed_memory(orc, combine):
     """mem=managed over several GPUs: one managed range per array, shards on 2 MiB boundaries."""

@@ -58,7 +58,7 @@ def time_blocking(fn, reps, warm=3, before=None):
     return best * 1e3
 
 
-def configs(kernel, quick):
+def configs(kernel, quick, hints_override=None):
     if kernel == "copy_async":
         for variant, stages, chunk, grid in itertools.product(("bulk", "tma"), (2, 3, 4, 6, 8), (8192, 16384, 32768, 49152, 65536),
                                                               (-1, -2, -3, -4)):
@@ -80,6 +80,8 @@ def configs(kernel, quick):
     if quick:
         hints = (1, 3)
         blocks = (256, 512, 1024) if kernel != "dot" else (256, 512)
+    if hints_override:
+        hints = hints_override
     for (v, u), b, g, h, var in itertools.product(vec_unroll, blocks, grids, hints, variants):
         if kernel == "dot" and b == 1024 and v * u >= 128:
             continue
@@ -149,11 +151,9 @@ def main():
             nbytes = bs.WEIGHTS[base] * n * eb
             best = []
             first_row = len(rows)
-            for kw in configs(kernel, args.quick):
+            for kw in configs(kernel, args.quick, tuple(int(h) for h in args.hints.split(",")) if args.hints else None):
                 if time.time() - t_start > args.budget_s:
                     break
-                if args.hints and str(kw.get("cache_hint")) not in args.hints.split(","):
-                    continue
                 pair = [bs.LaunchCfg.make(**kw), bs.LaunchCfg.make(flags=bs.LAUNCH_REVERSE if args.alternate else 0, **kw)]
                 turn = [0]
 
