@@ -147,10 +147,11 @@ __device__ __forceinline__ uint64_t make_policy() {
 //              last -- the part that is still in the 126 MB L2 (output lines not yet written back, inputs just read).
 //   keep_from  tiles p >= keep_from (dispatch order, i.e. the END of the sweep) load with evict_normal and store with
 //              evict_last instead of evict_first, so that the successor finds them.  Only with H_EVICT_FIRST (the other
-//              hints keep everything by default); ~0 = no tile.  Measured on B200 (profiles/r02/lab_zigzag.txt):
-//              2^25 fp64, six-kernel sequence of blocking calls: 655 us forward -> 635 us alternating -> 627 us with
-//              the last 96 MB kept; at 2^27 and beyond keeping HURTS (the kept lines take write-combining room from the
-//              stream: +2.6 % at 2^29), alternating alone still gains 0.3-0.6 %.
+//              hints keep everything by default); ~0 = no tile.  Measured on B200 (profiles/r02/lab_zigzag.txt,
+//              driver_session_e_sweep_keep.txt): 2^25 fp64, six-kernel sequence of blocking calls: 646 us forward ->
+//              638 us alternating -> 618 us with the last 128 MB kept; at 2^27 and beyond keeping HURTS (kept lines are
+//              never displaced by evict-first traffic and squat in L2: +2.6 % at 2^29) -- there every line gets the
+//              same priority and the alternation alone gains 0.5-1.2 % (which class does what: tuning.cu).
 // The elementwise kernels take the direction as an affine map, prepared by the launcher so that the per-block prologue
 // (the latency before a block's first load, which a one-tile-per-block grid pays 2^19 times at 2^29) stays short:
 // dispatch index p starts at vector origin + stride*p, stride = +-(vectors per tile).  p < 2^32 (checked on the host).

@@ -5,7 +5,7 @@
 // The reference fixes its shape at compile time: 256 threads, UNROLL_FACTOR 4 scalar accesses,
 // grid = ceil(N/4/256), dot = 4 blocks/SM x 1024 threads (src/cuda/CUDAStream.h:18-19,
 // CUDAStream.cu:126,196-198).  Here the shape is chosen per (kernel, bytes, L2 size); the
-// entries below are the winners of tools/sweep.py on a B200 (profiles/r01_sweep_*.csv).
+// entries below are the winners of tools/sweep.py on a B200 (profiles/r01/sweep_*_top.csv, profiles/r02/).
 #include <limits.h>
 #include <stdarg.h>
 #include <stdio.h>
