@@ -1047,16 +1047,39 @@ int b200_add(b200_ctx* ctx) { return run_kernel(ctx, B200_ADD, 0, 0, 0); }
 int b200_triad(b200_ctx* ctx, double scalar) { return run_kernel(ctx, B200_TRIAD, scalar, 0, 0); }
 int b200_nstream(b200_ctx* ctx, double scalar) { return run_kernel(ctx, B200_NSTREAM, scalar, 0, 0); }
 
+// dot_combine=host: the doorbells of the GPUs whose workers returned right after launching
+static int collect_deferred_dots(b200_ctx* ctx) {
+  for (Shard* s : ctx->shards) {
+    if (!s->dot_deferred) continue;
+    const int rc = bell_wait(s, s->dot_deferred, 8);
+    s->dot_deferred = 0;
+    if (rc) return rc;
+  }
+  return B200_OK;
+}
+
+int b200_warmup(b200_ctx* ctx, double scalar) {
+  if (!ctx) { set_error("null context"); return B200_EINVAL; }
+  if (int rc = managed_home(ctx)) return rc;
+  const int kernels[6] = {B200_COPY, B200_MUL, B200_ADD, B200_TRIAD, B200_DOT, B200_NSTREAM};
+  for (int reverse = 0; reverse < (ctx->alternate ? 2 : 1); reverse++) {
+    for (int k : kernels) {
+      Command cmd;
+      cmd.kind = CMD_KERNEL; cmd.kernel = k; cmd.reverse = reverse;
+      cmd.s0 = (k == B200_MUL || k == B200_TRIAD || k == B200_NSTREAM) ? scalar : 0.0; cmd.s1 = 0; cmd.s2 = 0;
+      if (int rc = run_all(ctx, cmd)) return rc;
+      if (k == B200_DOT) { if (int rc = collect_deferred_dots(ctx)) return rc; }
+    }
+  }
+  ctx->next_reverse = 0;
+  return B200_OK;
+}
+
 int b200_dot(b200_ctx* ctx, double* result) {
   if (int rc = run_kernel(ctx, B200_DOT, 0, 0, 0)) return rc;
   double total;
   if (ctx->ngpus > 1 && ctx->combine == COMBINE_HOST) {
-    for (Shard* s : ctx->shards) {
-      if (!s->dot_deferred) continue;
-      const int rc = bell_wait(s, s->dot_deferred, 8);
-      s->dot_deferred = 0;
-      if (rc) return rc;
-    }
+    if (int rc = collect_deferred_dots(ctx)) return rc;
     // G values, added in rank order in type T: deterministic
     if (ctx->elem_bytes == 8) { double t = 0; for (Shard* s : ctx->shards) t += *static_cast<volatile double*>(s->dot_host); total = t; }
     else { float t = 0; for (Shard* s : ctx->shards) t += *static_cast<volatile float*>(s->dot_host); total = t; }

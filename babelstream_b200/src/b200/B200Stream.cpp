@@ -52,6 +52,9 @@ B200Stream<T>::B200Stream(BenchId bs, const intptr_t array_size, const int devic
   char desc[4096] = "";
   if (b200_describe(ctx, desc, (int)sizeof desc) == B200_OK) std::cout << desc;
 
+  // First-use costs (lazy loading of each kernel's code, launch plans) are paid here, not inside the first timed call:
+  // --order Isolated averages over every call of a kernel (src/main.cpp:168-175).  Contents undefined until init_arrays.
+  check(b200_warmup(ctx, startScalar), "warmup");
   init_arrays(initA, initB, initC);
 }
 

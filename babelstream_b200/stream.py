@@ -131,6 +131,7 @@ def lib() -> C.CDLL:
         "b200_set_option": (ci, [vp, cp, cp]),
         "b200_describe": (ci, [vp, cp, ci]),
         "b200_init_arrays": (ci, [vp, d, d, d]),
+        "b200_warmup": (ci, [vp, d]),
         "b200_copy": (ci, [vp]),
         "b200_mul": (ci, [vp, d]),
         "b200_add": (ci, [vp]),
@@ -434,6 +435,10 @@ class B200Stream:
         """One process per GPU: dot() returns the all-rank sum from here on (fused peer-memory all-reduce)."""
         boxes = (C.c_void_p * max(1, len(mailboxes)))(*mailboxes)
         _check(lib().b200_join_group(self._h, world, rank, boxes))
+
+    def warmup(self, scalar: float = START_SCALAR) -> None:
+        """Pays every kernel's first-use cost now (code loading, launch plans); array contents become undefined."""
+        _check(lib().b200_warmup(self._h, C.c_double(scalar)))
 
     def describe(self) -> str:
         buf = C.create_string_buffer(4096)

@@ -264,6 +264,14 @@ int b200_join_group(b200_ctx* ctx, int world, int rank, void* const* mailboxes);
 int b200_set_option(b200_ctx* ctx, const char* key, const char* value);
 int b200_describe(b200_ctx* ctx, char* buf, int buflen); /* human-readable configuration, for the model's banner */
 
+/* Makes the FIRST call of every kernel as cheap as the later ones: runs copy, mul, add, triad, dot, nstream once in each
+ * sweep direction with this scalar, so that their code is loaded (CUDA loads a kernel lazily at its first launch:
+ * 1.5-4 ms per elementwise kernel, 37 ms for dot) and their launch plans are captured.  The driver's Classic order
+ * drops the first iteration from its statistics, but --order Isolated (src/main.cpp:168-175) averages over ALL calls of
+ * a kernel; the model's constructor therefore calls this.  The arrays' contents are undefined afterwards: call it before
+ * init_arrays / write_arrays. */
+int b200_warmup(b200_ctx* ctx, double scalar);
+
 int b200_init_arrays(b200_ctx* ctx, double init_a, double init_b, double init_c); /* Stream::init_arrays */
 int b200_copy(b200_ctx* ctx);                                                     /* Stream::copy     c = a */
 int b200_mul(b200_ctx* ctx, double scalar);                                       /* Stream::mul      b = s*c */

@@ -65,6 +65,35 @@ def test_known_answers_every_row(orc, golden_rows):
         s.close()
 
 
+def test_warmup_pays_first_use_costs_and_leaves_results_alone(orc):
+    """b200_warmup (called by the model's constructor): afterwards the FIRST call of every kernel costs what the later
+    ones do -- --order Isolated (src/main.cpp:168-175) averages over all of them -- and a run gives the usual bits."""
+    import time
+    n = (1 << 20) + 3
+    with bs.B200Stream(n, dtype=np.float64) as s:
+        s.warmup()
+        s.init_arrays()
+        first = {}
+        for k in ORDER:
+            t0 = time.perf_counter()
+            s.run(k)
+            first[k] = time.perf_counter() - t0
+        # unwarmed: 1.7-3.9 ms per elementwise kernel, 38 ms for dot (profiles/r02/first_call_costs_session_n.txt)
+        assert max(first.values()) < 1e-3, first
+        s.init_arrays()
+        total = drive(s, orc, O.ALL, O.ORDER_ISOLATED, 6)
+        a, b, c = s.get_arrays()
+        g = orc.gold(np.float64, O.ALL, O.ORDER_ISOLATED, 6, n)
+        assert bits(a[0]) == bits(g[0]) and bits(b[-1]) == bits(g[1]) and bits(c[n // 2]) == bits(g[2])
+        assert orc.check_solution(O.ALL, O.ORDER_ISOLATED, 6, a, b, c, total) == 0
+        s.set_option("sweep", "forward")      # plans are rebuilt on their next use; a second warm-up is legal any time
+        s.warmup(0.4)
+        s.init_arrays()
+        total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 3)
+        a, b, c = s.get_arrays()
+        assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 3, a, b, c, total) == 0
+
+
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("n", [1, 100, 33554432 // 32 + 5])
 def test_check_solution_passes(orc, dtype, n):
