@@ -166,9 +166,26 @@ def parse_stream_csv(text: str):
 _START_AFFINITY = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
 
 
-def _restore_affinity():
-    if _START_AFFINITY:
-        os.sched_setaffinity(0, _START_AFFINITY)
+class _start_affinity:
+    """Runs a child with the CPU mask this program was started with (the mask is inherited at fork from the calling
+    thread; set around the call rather than in a preexec_fn, which is unsafe in a process with other threads)."""
+
+    def __enter__(self):
+        self.saved = None
+        if _START_AFFINITY:
+            try:
+                self.saved = os.sched_getaffinity(0)
+                os.sched_setaffinity(0, _START_AFFINITY)
+            except OSError:
+                self.saved = None
+
+    def __exit__(self, *exc):
+        if self.saved:
+            try:
+                os.sched_setaffinity(0, self.saved)
+            except OSError:
+                pass
+        return False
 
 
 def run_stream_binary(path, n, num_times, only="All", env=None, timeout=900, want_wall=False):
@@ -176,8 +193,9 @@ def run_stream_binary(path, n, num_times, only="All", env=None, timeout=900, wan
     e = dict(os.environ)
     e.update(env or {})
     t0 = time.perf_counter()
-    p = subprocess.run([path, "--csv", "--gigabytes", "-s", str(n), "-n", str(num_times), "--only", only],
-                       capture_output=True, text=True, timeout=timeout, env=e, preexec_fn=_restore_affinity)
+    with _start_affinity():
+        p = subprocess.run([path, "--csv", "--gigabytes", "-s", str(n), "-n", str(num_times), "--only", only],
+                           capture_output=True, text=True, timeout=timeout, env=e)
     wall = time.perf_counter() - t0
     if p.returncode != 0:
         raise RuntimeError(f"{os.path.basename(path)} exited {p.returncode}: {p.stderr[-400:]}")
