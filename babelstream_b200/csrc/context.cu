@@ -301,8 +301,8 @@ static int build_plan(b200_ctx* ctx, Shard* s, const Command& cmd, const b200_do
   return B200_OK;
 }
 
-// Everything one GPU does for one command, including the wait.  Runs on the worker thread of the
-// shard (G > 1) or on the caller's thread (G == 1).
+// Everything one GPU does for one command, including the wait.  Runs on the caller's thread for
+// shard 0 and on the shard's worker thread for the others.
 static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
   Shard* s = ctx->shards[g];
   const size_t eb = (size_t)ctx->elem_bytes;
