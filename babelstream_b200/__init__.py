@@ -37,10 +37,12 @@ from .stream import (  # noqa: F401
     device_count,
     launch_count,
     resolve_cfg,
+    plan_sweep,
+    SweepPlan,
     shard_range,
 )
 
 __all__ = ["B200Error", "B200Stream", "LaunchCfg", "Doorbell", "Mailbox", "lib", "lib_path", "launch", "launch_dot",
            "launch_dot_allreduce_p2p", "launch_dot_send_p2p", "launch_dot_collect_p2p", "launch_doorbell", "launch_dot_doorbell",
-           "dot_workspace_bytes", "dot_status_offset", "set_p2p_timeout_ms", "LAUNCH_PDL", "LAUNCH_REVERSE", "LAUNCH_DOT_GRIDSTRIDE", "ETIMEOUT", "device_count", "launch_count", "resolve_cfg", "shard_range",
+           "dot_workspace_bytes", "dot_status_offset", "set_p2p_timeout_ms", "LAUNCH_PDL", "LAUNCH_REVERSE", "LAUNCH_DOT_GRIDSTRIDE", "ETIMEOUT", "device_count", "launch_count", "resolve_cfg", "plan_sweep", "SweepPlan", "shard_range",
            "KERNELS", "KERNEL_IDS", "WEIGHTS", "HINTS", "VARIANTS"]

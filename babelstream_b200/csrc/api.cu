@@ -130,13 +130,12 @@ int launch_ew(int kernel, void* a, void* b, void* c, size_t n, int elem_bytes, d
   }
   call.g = make_geometry(need_a ? a : nullptr, need_b ? b : nullptr, c, n, elem_bytes, call.r.vec_bytes, call.r.block,
                          call.r.unroll, call.r.cache_hint);
-  call.grid = grid_for(call.r.grid_policy, call.g.ntiles, props->num_sms);
-  call.reverse = (call.r.flags & B200_LAUNCH_REVERSE) != 0;
-  {
-    const int arrays = (kernel == B200_COPY || kernel == B200_MUL) ? 2 : kernel == B200_NSTREAM ? 4 : 3;
-    const double tile_bytes = (double)call.r.block * call.g.unroll * call.g.vec_bytes * arrays;
-    call.keep_from = keep_from_for(call.r.keep_mb, call.g.cache_hint, call.g.ntiles, tile_bytes);
+  if (call.g.ntiles >> 32) {
+    set_error("launch shape gives %llu tiles (2^32 or more): use a larger block or unroll", (unsigned long long)call.g.ntiles);
+    return B200_EINVAL;
   }
+  call.sweep = plan_sweep(kernel, call.r, call.g, props->num_sms);
+  call.grid = call.sweep.grid;
   switch (kernel) {
     case B200_INIT: return launch_ew_init(call);
     case B200_COPY: return launch_ew_copy(call);
@@ -171,17 +170,8 @@ int launch_dot_common(const void* a, const void* b, size_t n, int elem_bytes, vo
   if (bell) { call.bell.flag = bell->flag_host_mapped; call.bell.seq = bell->seq; }
   call.stream = static_cast<cudaStream_t>(stream);
   call.g = make_geometry(a, b, nullptr, n, elem_bytes, call.r.vec_bytes, call.r.block, call.r.unroll, call.r.cache_hint);
-  call.grid = grid_for(call.r.grid_policy, call.g.ntiles, props->num_sms);
-  if (!(call.r.flags & B200_LAUNCH_DOT_GRIDSTRIDE) && call.g.ntiles > 0) {
-    // one contiguous chunk of k tiles per logical block; no empty blocks
-    const unsigned long long k = (call.g.ntiles + call.grid - 1) / call.grid;
-    call.tiles_per_block = (unsigned)k;
-    call.grid = (unsigned)((call.g.ntiles + k - 1) / k);
-  }
-  call.reverse = (call.r.flags & B200_LAUNCH_REVERSE) != 0;
-  call.keep_from = keep_from_for(call.r.keep_mb, call.g.cache_hint, call.grid,
-                                 (double)(call.tiles_per_block ? call.tiles_per_block : 1) * call.r.block * call.g.unroll *
-                                     call.g.vec_bytes * 2.0);
+  call.sweep = plan_sweep(B200_DOT, call.r, call.g, props->num_sms);
+  call.grid = call.sweep.grid;
   return launch_dot_impl(call);
 }
 

@@ -48,9 +48,9 @@ static int launch_dot_typed(const DotCall& call) {
   args.partials = call.workspace;
   args.result_dev = call.result_dev; args.result_host = call.result_host;
   args.nvec = call.g.nvec; args.ntiles = call.g.ntiles; args.n = call.n; args.head = call.g.head;
-  args.tiles_per_block = call.tiles_per_block;
-  args.sweep.reverse = call.reverse ? 1u : 0u;
-  args.sweep.keep_from = call.keep_from >= 0xffffffffull ? ~0u : (unsigned)call.keep_from;
+  args.tiles_per_block = call.sweep.tiles_per_block;
+  args.sweep.reverse = call.sweep.reverse ? 1u : 0u;
+  args.sweep.keep_from = call.sweep.keep_from >= 0xffffffffull ? ~0u : (unsigned)call.sweep.keep_from;
   args.sweep.origin = 0; args.sweep.stride = 0;
   args.bell_flag = static_cast<unsigned long long*>(call.bell.flag); args.bell_seq = call.bell.seq;
   args.seq_counters = static_cast<unsigned long long*>(call.seq_counters);
@@ -82,6 +82,7 @@ int launch_dot_impl(const DotCall& call) {
       return B200_EINVAL;
     }
   }
+  static_assert(kDotMaxPartials == (unsigned)kDotMaxBlocks, "host and device disagree about the dot workspace");
   if (call.grid > (unsigned)kDotMaxBlocks) {
     set_error("dot grid %u exceeds the workspace capacity of %d blocks", call.grid, kDotMaxBlocks);
     return B200_EINVAL;

@@ -97,6 +97,23 @@ struct Geometry {
 Geometry make_geometry(const void* p0, const void* p1, const void* p2, size_t n, int elem_bytes, int vec_bytes,
                        int block, int unroll, int cache_hint);
 
+// How a grid walks its tiles (pure host logic, tuning.cu; unit-tested without a GPU through b200_plan_sweep).
+//   elementwise: dispatch index p in [0, ntiles) starts at vector origin + stride*p (blocks take p = blockIdx.x,
+//                blockIdx.x + grid, ...); p >= keep_from keeps its lines in L2.
+//   dot:         logical block L in [0, grid) owns tiles [L*tiles_per_block, min((L+1)*tiles_per_block, ntiles))
+//                (tiles_per_block = 0: grid-stride L, L+grid, ...); dispatch index p is L, or grid-1-L when reversed;
+//                p >= keep_from loads with evict-normal.
+constexpr unsigned kDotMaxPartials = 16384;  // == kDotMaxBlocks (kernels.cuh): block partials the dot workspace holds
+struct SweepPlan {
+  unsigned grid = 1;
+  unsigned tiles_per_block = 0;
+  bool reverse = false;
+  unsigned long long keep_from = ~0ull;  // ~0: no keep region
+  unsigned long long origin = 0;
+  long long stride = 0;
+};
+SweepPlan plan_sweep(int kernel, const Resolved& r, const Geometry& g, int num_sms);
+
 // Completion doorbell of a launch (see kernels.cuh); flag == nullptr: none.
 struct Bell {
   void* ticket = nullptr;      // device word, zero between launches
@@ -115,8 +132,7 @@ struct EwCall {
   unsigned grid;
   cudaStream_t stream;
   Bell bell;
-  bool reverse = false;                     // sweep from the top down (B200_LAUNCH_REVERSE)
-  unsigned long long keep_from = ~0ull;     // tiles (dispatch order) from here on keep their lines in L2
+  SweepPlan sweep;                          // direction, keep region (plan_sweep)
 };
 int launch_ew_init(const EwCall& call);
 int launch_ew_copy(const EwCall& call);
@@ -143,9 +159,7 @@ struct DotCall {
   Resolved r;
   Geometry g;
   unsigned grid;
-  unsigned tiles_per_block = 0;             // > 0: contiguous chunk per logical block; 0: grid-stride
-  bool reverse = false;
-  unsigned long long keep_from = ~0ull;     // blocks (dispatch order) from here on load with evict_normal
+  SweepPlan sweep;                          // chunking, direction, keep region (plan_sweep)
   cudaStream_t stream;
 };
 int launch_dot_impl(const DotCall& call);

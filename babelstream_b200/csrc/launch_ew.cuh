@@ -41,15 +41,10 @@ int launch_ew_typed(const EwCall& call) {
   args.va = static_cast<char*>(call.a) + head_bytes;
   args.vb = static_cast<char*>(call.b) + head_bytes;
   args.vc = static_cast<char*>(call.c) + head_bytes;
-  if (call.g.ntiles >> 32) {
-    set_error("launch shape gives %llu tiles (2^32 or more): use a larger block or unroll", (unsigned long long)call.g.ntiles);
-    return B200_EINVAL;
-  }
-  const unsigned long long tile_vecs = (unsigned long long)call.r.block * (unsigned)u;
-  args.sweep.reverse = call.reverse ? 1u : 0u;
-  args.sweep.origin = call.reverse && call.g.ntiles ? (call.g.ntiles - 1) * tile_vecs : 0;
-  args.sweep.stride = call.reverse ? -(long long)tile_vecs : (long long)tile_vecs;
-  args.sweep.keep_from = call.keep_from >= 0xffffffffull ? ~0u : (unsigned)call.keep_from;
+  args.sweep.reverse = call.sweep.reverse ? 1u : 0u;
+  args.sweep.origin = call.sweep.origin;
+  args.sweep.stride = call.sweep.stride;
+  args.sweep.keep_from = call.sweep.keep_from >= 0xffffffffull ? ~0u : (unsigned)call.sweep.keep_from;
   args.bell.ticket = static_cast<unsigned int*>(call.bell.ticket);
   args.bell.flag = static_cast<unsigned long long*>(call.bell.flag);
   args.bell.seq = call.bell.seq;

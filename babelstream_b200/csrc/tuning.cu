@@ -196,6 +196,30 @@ unsigned long long keep_from_for(int keep_mb, int cache_hint, unsigned long long
   return units - keep;
 }
 
+SweepPlan plan_sweep(int kernel, const Resolved& r, const Geometry& g, int num_sms) {
+  SweepPlan sp;
+  sp.grid = grid_for(r.grid_policy, g.ntiles, num_sms);
+  sp.reverse = (r.flags & B200_LAUNCH_REVERSE) != 0;
+  const double vec_tile_bytes = (double)r.block * g.unroll * g.vec_bytes;  // one tile of one array
+  if (kernel == B200_DOT) {
+    if (!(r.flags & B200_LAUNCH_DOT_GRIDSTRIDE) && g.ntiles > 0) {
+      // one contiguous chunk of k tiles per logical block; no empty blocks
+      const unsigned long long k = (g.ntiles + sp.grid - 1) / sp.grid;
+      sp.tiles_per_block = (unsigned)k;
+      sp.grid = (unsigned)((g.ntiles + k - 1) / k);
+    }
+    sp.keep_from = keep_from_for(r.keep_mb, g.cache_hint, sp.grid,
+                                 (double)(sp.tiles_per_block ? sp.tiles_per_block : 1) * vec_tile_bytes * 2.0);
+    return sp;
+  }
+  const int arrays = (kernel == B200_COPY || kernel == B200_MUL) ? 2 : kernel == B200_NSTREAM ? 4 : 3;
+  sp.keep_from = keep_from_for(r.keep_mb, g.cache_hint, g.ntiles, vec_tile_bytes * arrays);
+  const unsigned long long tile_vecs = (unsigned long long)r.block * (unsigned)g.unroll;
+  sp.origin = sp.reverse && g.ntiles ? (g.ntiles - 1) * tile_vecs : 0;
+  sp.stride = sp.reverse ? -(long long)tile_vecs : (long long)tile_vecs;
+  return sp;
+}
+
 Geometry make_geometry(const void* p0, const void* p1, const void* p2, size_t n, int elem_bytes, int vec_bytes,
                        int block, int unroll, int cache_hint) {
   Geometry g;
@@ -270,8 +294,28 @@ int b200_resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_b
     // geometry for perfectly aligned arrays
     const b200::Geometry g = b200::make_geometry(nullptr, nullptr, nullptr, n, elem_bytes, r.vec_bytes, r.block,
                                                  r.unroll, r.cache_hint);
-    *grid_out = b200::grid_for(r.grid_policy, g.ntiles, num_sms > 0 ? num_sms : 148);
+    *grid_out = b200::plan_sweep(kernel, r, g, num_sms > 0 ? num_sms : 148).grid;
   }
+  return B200_OK;
+}
+
+int b200_plan_sweep(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
+                    b200_sweep_plan* out) {
+  if (!out) { b200::set_error("b200_plan_sweep: null output"); return B200_EINVAL; }
+  b200::Resolved r;
+  if (int rc = b200::resolve_cfg(kernel, n, elem_bytes, num_sms, l2_bytes, in, &r)) return rc;
+  const b200::Geometry g = b200::make_geometry(nullptr, nullptr, nullptr, n, elem_bytes, r.vec_bytes, r.block, r.unroll,
+                                               r.cache_hint);
+  const b200::SweepPlan sp = b200::plan_sweep(kernel, r, g, num_sms > 0 ? num_sms : 148);
+  if (kernel == B200_DOT && sp.grid > b200::kDotMaxPartials) {  // the launcher refuses the same way
+    b200::set_error("dot grid %u exceeds the workspace capacity of %u blocks", sp.grid, b200::kDotMaxPartials);
+    return B200_EINVAL;
+  }
+  memset(out, 0, sizeof *out);
+  out->grid = sp.grid; out->tiles_per_block = sp.tiles_per_block; out->reverse = sp.reverse ? 1 : 0;
+  out->keep_from = sp.keep_from; out->origin = sp.origin; out->stride = sp.stride;
+  out->ntiles = g.ntiles; out->nvec = g.nvec; out->tile_vecs = (unsigned long long)r.block * (unsigned)g.unroll;
+  out->vec_bytes = g.vec_bytes; out->unroll = g.unroll; out->cache_hint = g.cache_hint;
   return B200_OK;
 }
 

@@ -66,6 +66,13 @@ class LaunchCfg(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
 
 
+class SweepPlan(C.Structure):
+    """b200_sweep_plan: the walk a launch makes over its tiles (host logic, no GPU needed)."""
+    _fields_ = [("grid", C.c_uint), ("tiles_per_block", C.c_uint), ("reverse", C.c_int), ("vec_bytes", C.c_int),
+                ("unroll", C.c_int), ("cache_hint", C.c_int), ("keep_from", C.c_ulonglong), ("origin", C.c_ulonglong), ("stride", C.c_longlong),
+                ("ntiles", C.c_ulonglong), ("nvec", C.c_ulonglong), ("tile_vecs", C.c_ulonglong)]
+
+
 class Doorbell(C.Structure):
     """b200_doorbell: the kernel's last block stores `seq` to a mapped pinned host word."""
     _fields_ = [("ticket", C.c_void_p), ("flag_host_mapped", C.c_void_p), ("seq", C.c_ulonglong)]
@@ -101,6 +108,7 @@ def lib() -> C.CDLL:
         "b200_launch_count": (C.c_uint64, []),
         "b200_shard_range": (ci, [sz, ci, ci, ci, C.POINTER(sz), C.POINTER(sz)]),
         "b200_resolve_cfg": (ci, [ci, sz, ci, ci, ci, cfgp, cfgp, C.POINTER(C.c_uint)]),
+        "b200_plan_sweep": (ci, [ci, sz, ci, ci, ci, cfgp, C.POINTER(SweepPlan)]),
         "b200_launch_init": (ci, [vp, vp, vp, sz, ci, d, d, d, cfgp, vp]),
         "b200_launch_copy": (ci, [vp, vp, sz, ci, cfgp, vp]),
         "b200_launch_mul": (ci, [vp, vp, sz, ci, d, cfgp, vp]),
@@ -196,6 +204,14 @@ def resolve_cfg(kernel: str, n: int, elem_bytes: int, num_sms: int = 148, l2_byt
     _check(lib().b200_resolve_cfg(KERNEL_IDS[kernel], n, elem_bytes, num_sms, l2_bytes,
                                   C.byref(cfg) if cfg is not None else None, C.byref(out), C.byref(grid)))
     return out, grid.value
+
+
+def plan_sweep(kernel: str, n: int, elem_bytes: int, num_sms: int = 148, l2_bytes: int = 126 << 20,
+               cfg: LaunchCfg | None = None) -> SweepPlan:
+    out = SweepPlan()
+    _check(lib().b200_plan_sweep(KERNEL_IDS[kernel], n, elem_bytes, num_sms, l2_bytes,
+                                 C.byref(cfg) if cfg is not None else None, C.byref(out)))
+    return out
 
 
 def launch(kernel: str, a: int, b: int, c: int, n: int, elem_bytes: int, *, scalar: float = START_SCALAR,

@@ -116,6 +116,21 @@ int b200_shard_range(size_t n, int elem_bytes, int ngpus, int g, size_t* begin, 
  * fills `out`, and the resulting grid size / tile count. */
 int b200_resolve_cfg(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes,
                      const b200_launch_cfg* in, b200_launch_cfg* out, unsigned* grid_out);
+/* The walk a launch with this configuration makes over its tiles (vector-aligned arrays assumed), for inspection and
+ * tests.  Elementwise kernels: dispatch index p in [0, ntiles) -- block b takes p = b, b + grid, ... -- starts at vector
+ * origin + stride*p and covers tile_vecs vectors of vec_bytes bytes; p >= keep_from keeps its lines in L2
+ * (keep_from = ~0: none).  dot: logical block L in [0, grid) owns tiles [L*tiles_per_block, (L+1)*tiles_per_block)
+ * (tiles_per_block = 0: L, L + grid, ...); reverse only changes the order in which the logical blocks are dispatched. */
+typedef struct b200_sweep_plan {
+  unsigned grid, tiles_per_block;
+  int reverse, vec_bytes;
+  int unroll, cache_hint; /* as launched: 4 / default when the scalar path is taken (vec_bytes == elem_bytes) */
+  unsigned long long keep_from, origin;
+  long long stride;
+  unsigned long long ntiles, nvec, tile_vecs;
+} b200_sweep_plan;
+int b200_plan_sweep(int kernel, size_t n, int elem_bytes, int num_sms, int l2_bytes, const b200_launch_cfg* in,
+                    b200_sweep_plan* out);
 
 /* ------------------------------------------------------------------------------------------
  * LEVEL 1 -- raw launchers: one kernel on caller-owned DEVICE pointers, asynchronous on

@@ -90,7 +90,7 @@ def test_resolve_cfg_defaults_and_overrides():
     small, _ = bs.resolve_cfg("triad", 1 << 20, 8)   # 3 x 8 MB lives in the 126 MB L2
     assert small.cache_hint == bs.HINTS["default"], "no evict-first / no-allocate hints for an L2-resident working set"
     dot, grid = bs.resolve_cfg("dot", 1 << 25, 8)
-    assert dot.variant in (1, 2) and 0 < grid <= 4096 and grid % 148 == 0
+    assert dot.variant in (1, 2) and 7 * 148 < grid <= 8 * 148, "8 blocks per SM asked for, rounded to whole chunks of tiles"
     o, grid = bs.resolve_cfg("copy", 1 << 25, 4, cfg=bs.LaunchCfg.make(vec_bytes=16, unroll=8, block=128, grid=-3,
                                                                       cache_hint="stream", variant="bulk", contract="off"))
     assert (o.vec_bytes, o.unroll, o.block, o.grid, o.cache_hint, o.variant, o.contract) == (16, 8, 128, -3, 4, 2, 2)
@@ -384,3 +384,67 @@ def test_mailbox_bank_protocol_model():
                         assert slots[g][k & 1][s] == k
                         read[g][k & 1][s] = k
                 pc[g] += 1
+
+
+# ---------------------------------------------------------------------------------------------------
+# The walk of a launch over its tiles (csrc/tuning.cu: plan_sweep), the host half of the alternating sweep
+# ---------------------------------------------------------------------------------------------------
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+_shapes = st.sampled_from([(8, 1), (8, 2), (8, 4), (16, 1), (16, 2), (16, 4), (16, 8), (32, 1), (32, 2), (32, 4)])
+
+
+@settings(max_examples=300, deadline=None)
+@given(kernel=st.sampled_from(["copy", "mul", "add", "triad", "nstream", "init"]), log2n=st.integers(0, 33), jitter=st.integers(0, 4099),
+       shape=_shapes, block=st.sampled_from([32, 128, 256, 512]), grid=st.sampled_from([0, -1, -4, 7, 1000]),
+       reverse=st.booleans(), keep=st.sampled_from([0, -1, 1, 96, 4096]), hint=st.sampled_from([0, 1, 2, 3]), eb=st.sampled_from([4, 8]))
+def test_elementwise_sweep_covers_every_tile_once(kernel, log2n, jitter, shape, block, grid, reverse, keep, hint, eb):
+    n = (1 << log2n) + jitter
+    cfg = bs.LaunchCfg.make(vec_bytes=shape[0], unroll=shape[1], block=block, grid=grid, cache_hint=hint, keep_mb=keep,
+                            flags=bs.LAUNCH_REVERSE if reverse else 0)
+    try:
+        sp = bs.plan_sweep(kernel, n, eb, cfg=cfg)
+    except bs.B200Error:
+        return   # a shape the resolver refuses (covered by test_resolve_cfg_rejects)
+    r, _ = bs.resolve_cfg(kernel, n, eb, cfg=cfg)
+    tv = sp.tile_vecs
+    assert tv == r.block * sp.unroll and sp.ntiles == -(-sp.nvec // tv) and sp.nvec == n * eb // sp.vec_bytes
+    assert 1 <= sp.grid <= max(1, sp.ntiles) and sp.reverse == int(reverse)
+    if sp.ntiles:
+        # dispatch index p -> first vector origin + stride*p: p = 0 and p = ntiles-1 are the two ends, the map is affine,
+        # so every tile start t*tv, t in [0, ntiles), is hit exactly once
+        first, last = sp.origin, sp.origin + sp.stride * (sp.ntiles - 1)
+        assert abs(sp.stride) == tv
+        assert (first, last) == (((sp.ntiles - 1) * tv, 0) if reverse else (0, (sp.ntiles - 1) * tv))
+    # the keep region: only with the evict-first hint, the LAST tiles in dispatch order, keep_mb MB of traffic (or everything)
+    arrays = {"copy": 2, "mul": 2, "nstream": 4}.get(kernel, 3)
+    none = (1 << 64) - 1
+    if sp.cache_hint != bs.HINTS["evict_first"] or r.keep_mb <= 0 or sp.ntiles == 0:
+        assert sp.keep_from == none
+    else:
+        kept = sp.ntiles - sp.keep_from
+        want = r.keep_mb * 2 ** 20 / (tv * sp.vec_bytes * arrays)
+        assert 0 <= sp.keep_from <= sp.ntiles and (kept == sp.ntiles or want - 1 < kept <= want)
+
+
+@settings(max_examples=300, deadline=None)
+@given(log2n=st.integers(0, 33), jitter=st.integers(0, 4099), shape=_shapes, block=st.sampled_from([32, 128, 256, 512]),
+       grid=st.sampled_from([0, -1, -3, -8, -27, 5, 16384, 100000]), reverse=st.booleans(), stride_mode=st.booleans(),
+       eb=st.sampled_from([4, 8]), sms=st.sampled_from([1, 132, 148]))
+def test_dot_chunks_partition_the_tiles(log2n, jitter, shape, block, grid, reverse, stride_mode, eb, sms):
+    n = (1 << log2n) + jitter
+    flags = (bs.LAUNCH_REVERSE if reverse else 0) | (bs.LAUNCH_DOT_GRIDSTRIDE if stride_mode else 0)
+    cfg = bs.LaunchCfg.make(vec_bytes=shape[0], unroll=shape[1], block=block, grid=grid, flags=flags)
+    try:
+        sp = bs.plan_sweep("dot", n, eb, num_sms=sms, cfg=cfg)
+    except bs.B200Error as e:
+        assert "block must be" in str(e) or "unroll must be" in str(e) or "exceeds the workspace capacity" in str(e), str(e)
+        return
+    _, grid_out = bs.resolve_cfg("dot", n, eb, num_sms=sms, cfg=cfg)
+    assert grid_out == sp.grid, "b200_resolve_cfg reports the grid that is launched"
+    assert 1 <= sp.grid <= 16384, "the partials must fit the workspace (kDotMaxBlocks)"
+    if stride_mode or sp.ntiles == 0:
+        assert sp.tiles_per_block == 0
+        return
+    k = sp.tiles_per_block
+    assert k >= 1 and sp.grid * k >= sp.ntiles > (sp.grid - 1) * k, "every tile has exactly one owner and no block is empty"
