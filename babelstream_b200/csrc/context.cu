@@ -980,10 +980,13 @@ int b200_describe(b200_ctx* ctx, char* buf, int buflen) {
     Resolved r;
     if (resolve_cfg(k, ctx->shards[0]->count, ctx->elem_bytes, props->num_sms, props->l2_bytes, &ctx->tune[k], &r)) continue;
     const Geometry g = make_geometry(nullptr, nullptr, nullptr, ctx->shards[0]->count, ctx->elem_bytes, r.vec_bytes, r.block, r.unroll, r.cache_hint);
-    snprintf(line, sizeof line, "  %-8s vec %2dB unroll %d block %4d grid %-9u hint %d variant %d %s\n", names[k], r.vec_bytes,
-             r.unroll, r.block, grid_for(r.grid_policy, g.ntiles, props->num_sms), r.cache_hint, r.variant,
-             r.contract == 2 ? "unfused" : "fused");
+    const SweepPlan sp = plan_sweep(k, r, g, props->num_sms);
+    snprintf(line, sizeof line, "  %-8s vec %2dB unroll %d block %4d grid %-9u hint %d variant %d %s", names[k], r.vec_bytes,
+             r.unroll, r.block, sp.grid, r.cache_hint, r.variant, r.contract == 2 ? "unfused" : "fused");
     out += line;
+    if (sp.tiles_per_block) { snprintf(line, sizeof line, ", %u tiles per block", sp.tiles_per_block); out += line; }
+    if (sp.keep_from != ~0ull) { snprintf(line, sizeof line, ", last %d MB of a sweep kept in L2", r.keep_mb); out += line; }
+    out += "\n";
   }
   if (ctx->ngpus > 1) {
     int v = 0;
