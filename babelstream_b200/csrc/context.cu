@@ -1107,6 +1107,15 @@ int b200_run(b200_ctx* ctx, int kernel, double scalar, double* result) {
   return B200_EINVAL;
 }
 
+// Several blocking calls from one call: what the driver's loop over bench[] does (src/main.cpp:150-165), for hosts whose
+// own per-call overhead is not negligible (an interpreter).  Every kernel is launched and waited for before the next.
+int b200_run_sequence(b200_ctx* ctx, const int* kernels, int count, double scalar, double* last_dot) {
+  if (!ctx || (count > 0 && !kernels) || count < 0) { set_error("b200_run_sequence: bad arguments"); return B200_EINVAL; }
+  for (int i = 0; i < count; i++)
+    if (int rc = b200_run(ctx, kernels[i], scalar, last_dot)) return rc;
+  return B200_OK;
+}
+
 static int transfer(b200_ctx* ctx, int kind, void* a, void* b, void* c) {
   if (!ctx) { set_error("null context"); return B200_EINVAL; }
   Command cmd;

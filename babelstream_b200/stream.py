@@ -140,6 +140,7 @@ def lib() -> C.CDLL:
         "b200_describe": (ci, [vp, cp, ci]),
         "b200_init_arrays": (ci, [vp, d, d, d]),
         "b200_warmup": (ci, [vp, d]),
+        "b200_run_sequence": (ci, [vp, C.POINTER(ci), ci, d, C.POINTER(d)]),
         "b200_copy": (ci, [vp]),
         "b200_mul": (ci, [vp, d]),
         "b200_add": (ci, [vp]),
@@ -405,6 +406,17 @@ class B200Stream:
         if kernel == "dot":
             return self.dot()
         return getattr(self, kernel)(*(() if kernel in ("copy", "add") else (scalar,)))
+
+    def run_sequence(self, kernels, scalar=START_SCALAR):
+        """The given kernels as consecutive blocking calls issued from C (b200_run_sequence); returns the last dot or None."""
+        key = tuple(kernels)
+        cached = getattr(self, "_seq_cache", None)
+        if cached is None or cached[0] != key:
+            ids = (C.c_int * len(key))(*[KERNEL_IDS[k] for k in key])
+            self._seq_cache = cached = (key, ids, C.c_double(), "dot" in key)
+        _, ids, out, has_dot = cached
+        _check(lib().b200_run_sequence(self._h, ids, len(key), scalar, C.byref(out)))
+        return self.dtype.type(out.value) if has_dot else None
 
     def get_arrays(self):
         """Three numpy VIEWS of the library-owned host mirrors (valid until close), like get_arrays()."""

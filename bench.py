@@ -564,6 +564,10 @@ def main():
         join_group(s, dist, world, rank, boxes_e2e)   # dot() now returns the all-rank sum, one launch, no NCCL
 
     def e2e_step():
+        if combine != "nccl":
+            # six blocking calls issued from C (b200_run_sequence), like the driver's loop over bench[]: each kernel is
+            # launched and waited for before the next; only the interpreter's per-call cost (~1 us) is left out
+            return s.run_sequence(KERNEL_ORDER)
         for k in KERNEL_ORDER:
             if k == "dot":
                 v = s.dot()                       # device -> host: the sum, every step
@@ -720,7 +724,7 @@ def main():
                      "peak_source": peak_src},
         "e2e": {"value": round(world * step_bytes / (e2e_ms / K * 1e-3) / 1e9, 1), "unit": UNIT, "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": eb, "ms_per_step": round(e2e_ms / K, 5),
-                "how": "blocking b200_* Stream<T> calls timed with the host clock, as src/main.cpp:109-116 does; "
+                "how": "blocking b200_* Stream<T> calls (six per step, issued by b200_run_sequence) timed with the host clock, as src/main.cpp:109-116 does; "
                        "kernel arguments only on the way in, dot's sum read back every step; the arrays are device-resident "
                        "by the reference's design (src/Stream.h:29-49), see e2e_host_buffers and e2e_whole_run for the PCIe-inclusive views"},
         "parity": parity,

@@ -295,6 +295,9 @@ int b200_triad(b200_ctx* ctx, double scalar);                                   
 int b200_nstream(b200_ctx* ctx, double scalar);                                   /* Stream::nstream  a += b+s*c */
 int b200_dot(b200_ctx* ctx, double* result);                                      /* Stream::dot      sum a*b; value of type T widened to double */
 int b200_run(b200_ctx* ctx, int kernel, double scalar, double* result);           /* dispatch by kernel id */
+/* `count` blocking calls in the given order, each launched and waited for before the next -- the driver's loop over
+ * bench[] (src/main.cpp:150-165) in one call, for hosts with a costly foreign-function call.  *last_dot: the last dot. */
+int b200_run_sequence(b200_ctx* ctx, const int* kernels, int count, double scalar, double* last_dot);
 
 /* Stream::get_arrays (CUDAStream.cu:213-235): gathers all shards into library-owned host buffers
  * (pinned when they fit) that stay valid until b200_destroy. */

@@ -151,6 +151,23 @@ def test_write_read_roundtrip_and_random_parity(orc, dtype):
             assert abs(d - want) <= 64 * np.finfo(dtype).eps * scale
 
 
+def test_run_sequence_is_the_same_blocking_calls(orc):
+    """b200_run_sequence: the driver's loop over bench[] in one call -- same bits as six separate calls."""
+    n = (1 << 21) + 7
+    with bs.B200Stream(n, dtype=np.float64) as s, bs.B200Stream(n, dtype=np.float64) as t:
+        for _ in range(4):
+            v = s.run_sequence(ORDER)
+            for k in ORDER:
+                w = t.run(k)
+                if k == "dot":
+                    assert np.asarray(v).tobytes() == np.asarray(w).tobytes()
+        for x, y in zip(s.get_arrays(), t.get_arrays()):
+            assert x.tobytes() == y.tobytes()
+        assert s.run_sequence(["copy", "add"]) is None
+        with pytest.raises(bs.B200Error):
+            bs.stream._check(bs.lib().b200_run_sequence(s._h, None, 3, 0.4, None))
+
+
 def test_options_and_variants(orc):
     n = 1 << 20
     ref = None
