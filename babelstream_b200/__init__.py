@@ -22,6 +22,8 @@ from .stream import (  # noqa: F401
     lib_path,
     launch,
     launch_dot,
+    launch_dot_static,
+    DOT_STATIC_MAX_BLOCKS,
     launch_dot_allreduce_p2p,
     launch_dot_send_p2p,
     launch_dot_collect_p2p,
@@ -42,7 +44,7 @@ from .stream import (  # noqa: F401
     shard_range,
 )
 
-__all__ = ["B200Error", "B200Stream", "LaunchCfg", "Doorbell", "Mailbox", "lib", "lib_path", "launch", "launch_dot",
+__all__ = ["B200Error", "B200Stream", "LaunchCfg", "Doorbell", "Mailbox", "lib", "lib_path", "launch", "launch_dot", "launch_dot_static", "DOT_STATIC_MAX_BLOCKS",
            "launch_dot_allreduce_p2p", "launch_dot_send_p2p", "launch_dot_collect_p2p", "launch_doorbell", "launch_dot_doorbell",
            "dot_workspace_bytes", "dot_status_offset", "set_p2p_timeout_ms", "LAUNCH_PDL", "LAUNCH_REVERSE", "LAUNCH_DOT_GRIDSTRIDE", "ETIMEOUT", "device_count", "launch_count", "resolve_cfg", "plan_sweep", "SweepPlan", "shard_range",
            "KERNELS", "KERNEL_IDS", "WEIGHTS", "HINTS", "VARIANTS"]

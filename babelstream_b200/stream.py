@@ -117,6 +117,7 @@ def lib() -> C.CDLL:
         "b200_launch_nstream": (ci, [vp, vp, vp, sz, ci, d, cfgp, vp]),
         "b200_dot_workspace_bytes": (sz, []),
         "b200_launch_dot": (ci, [vp, vp, sz, ci, vp, vp, vp, cfgp, vp]),
+        "b200_launch_dot_static": (ci, [vp, vp, sz, ci, vp, vp, cfgp, vp]),
         "b200_dot_mailbox_bytes": (sz, []),
         "b200_launch_dot_allreduce_p2p": (ci, [vp, vp, sz, ci, vp, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
         "b200_launch_dot_send_p2p": (ci, [vp, vp, sz, ci, vp, vp, ci, ci, C.c_ulonglong, C.POINTER(vp), cfgp, vp]),
@@ -243,6 +244,24 @@ def launch_dot(a: int, b: int, n: int, elem_bytes: int, workspace: int, result_d
     """LEVEL 1: enqueue dot; the sum (type T) lands in result_dev.  Asynchronous."""
     _check(lib().b200_launch_dot(a, b, n, elem_bytes, workspace, result_dev or None, result_host_mapped or None,
                                  C.byref(cfg) if cfg is not None else None, C.c_void_p(stream)))
+
+
+DOT_STATIC_MAX_BLOCKS = 16384  # B200_DOT_STATIC_MAX_BLOCKS
+
+
+def launch_dot_static(a: int, b: int, n: int, elem_bytes: int, result_dev: int, *, result_host_mapped: int = 0,
+                      cfg: LaunchCfg | None = None, stream: int = 0) -> None:
+    """LEVEL 1: dot for callers that have no workspace to give and may not allocate one.
+
+    ``launch_dot`` needs a zeroed device buffer from the caller.  A binding that only forwards device addresses and
+    has no CUDA runtime of its own, a service that keeps cudaMalloc (a device-wide synchronisation) out of its steady
+    state, or a process whose device memory is fully handed out cannot produce one.  This call keeps the partials in
+    an array inside the library image instead and allocates nothing; same bits as ``launch_dot``.  One array per GPU:
+    do not let two of these calls overlap on the device, stay within ``DOT_STATIC_MAX_BLOCKS`` blocks, and make the
+    first call on a GPU outside stream capture (it looks the array's address up).  Asynchronous on ``stream``.
+    """
+    _check(lib().b200_launch_dot_static(a, b, n, elem_bytes, result_dev or None, result_host_mapped or None,
+                                        C.byref(cfg) if cfg is not None else None, C.c_void_p(stream)))
 
 
 def launch_dot_allreduce_p2p(a: int, b: int, n: int, elem_bytes: int, workspace: int, result_dev: int, *, world: int,

@@ -161,6 +161,34 @@ size_t b200_dot_workspace_bytes(void);
 int b200_launch_dot(const void* a, const void* b, size_t n, int elem_bytes, void* workspace, void* result_dev,
                     void* result_host_mapped, const b200_launch_cfg* cfg, void* stream);
 
+/* dot WITHOUT a caller-supplied workspace, and without any allocation inside the library.  This one has no counterpart
+ * in the reference (its model allocates the block sums in its constructor, CUDAStream.cu:128-145); it exists for the
+ * callers of this ABI that cannot give b200_launch_dot the zeroed cudaMalloc'ed workspace it asks for:
+ *   - bindings that are handed device addresses by their host program but do not link the CUDA runtime themselves,
+ *     so they have nothing to allocate with;
+ *   - services that keep the allocator out of their steady state, because cudaMalloc/cudaFree synchronise the whole
+ *     device and stall every other stream;
+ *   - processes whose device memory was handed out completely at start-up, where a later allocation just fails.
+ * The block partials, tickets and group sums live in an array that is part of the library image instead
+ * (B200_DOT_STATIC_SCRATCH_BYTES per GPU; every GPU that loads the library's code keeps its copy until the process
+ * exits).  Same kernel, same summation order, hence the same bits as b200_launch_dot for equal (n, cfg, alignment).
+ * Rules:
+ *   - at most B200_DOT_STATIC_MAX_BLOCKS blocks: the automatic grid never comes near it, whatever n; a cfg whose grid
+ *     asks for more (an explicit block count on a long vector) is refused with B200_EINVAL;
+ *   - all calls on one GPU share the one array: calls that may overlap on the GPU (different streams with no ordering
+ *     between them) race and return garbage -- keep them on one stream or order them with events; concurrent dots need
+ *     b200_launch_dot with a workspace each;
+ *   - the first call on each GPU looks the array's device address up (cudaGetSymbolAddress with that GPU current) and
+ *     caches it: make that first call before any stream capture begins;
+ *   - the ticket region is cleared on `stream` ahead of every launch (cudaMemsetAsync), so a previous call that died
+ *     half-way cannot poison the next one;
+ *   - at least one of result_dev / result_host_mapped must be given.
+ * Calls no cudaMalloc, cudaFree or other allocating routine. */
+#define B200_DOT_STATIC_MAX_BLOCKS 16384
+#define B200_DOT_STATIC_SCRATCH_BYTES 139776
+int b200_launch_dot_static(const void* a, const void* b, size_t n, int elem_bytes, void* result_dev,
+                           void* result_host_mapped, const b200_launch_cfg* cfg, void* stream);
+
 /* Fused dot + all-reduce over NVLink peer memory: ONE launch per GPU, no NCCL.  GPU `rank` of `world`
  * (<= 8) computes its partial as b200_launch_dot does; the last block then stores it into slot `rank`
  * of every GPU's mailbox (peer stores), waits for the `world` partials of this call in its own
