@@ -18,6 +18,8 @@
 // default inside one process), inside the dot kernel by peer stores over NVLink (p2p: what process groups
 // use, b200_join_group) or by ONE ncclAllReduce of count 1 (nccl).
 #include <ctype.h>
+#include <errno.h>
+#include <limits.h>
 #include <dlfcn.h>
 #include <sched.h>
 #include <nccl.h>  // types only: the library is dlopen'ed, so single-GPU use needs no NCCL at all
@@ -107,6 +109,7 @@ struct Shard {
     uint64_t gen = 0;            // ctx->tune_gen it was built under
     unsigned nlaunch = 0;        // kernel nodes (for b200_launch_count)
     bool bell = false;           // dot: built with the doorbell
+    uint64_t timeout_gen = 0;    // p2p_timeout_gen() it was built under: the wait bound is a kernel parameter
   } plans[B200_NUM_KERNELS][2];  // [kernel][sweep direction]
   void* mailbox = nullptr;       // p2p combine: kMaxPeers slots in this GPU's HBM, written by the peers
   int rank = 0;
@@ -296,6 +299,7 @@ static int build_plan(b200_ctx* ctx, Shard* s, const Command& cmd, const b200_do
   p->graph = graph;
   p->s0 = cmd.s0; p->s1 = cmd.s1; p->s2 = cmd.s2;
   p->gen = ctx->tune_gen;
+  p->timeout_gen = p2p_timeout_gen();
   p->nlaunch = n;
   p->bell = bell != nullptr;
   return B200_OK;
@@ -329,7 +333,8 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
     b200_doorbell bell_store, *bell = nullptr;
     unsigned long long want = 0;
     int flag_off = 8;
-    if (is_dot && launches) want = ++s->dot_bell_seq;  // the kernel bumps seq_counters[0] on every launch
+    // the kernel bumps seq_counters[0] on every launch that RUNS: the host copy follows only once the launch went through
+    if (is_dot && launches) want = s->dot_bell_seq + 1;
     if (use_doorbell(ctx, s, cmd.kernel)) {
       if (is_dot) {  // value: the device-side counter
         bell_store.ticket = nullptr;
@@ -347,7 +352,7 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
     const bool replay = ctx->use_graphs && launches && !ctx->timing && !nccl_dot && !(bell && !is_dot);
     if (replay) {
       Shard::Plan& p = s->plans[cmd.kernel][cmd.reverse ? 1 : 0];
-      if (!p.exec || p.gen != ctx->tune_gen || p.s0 != cmd.s0 || p.s1 != cmd.s1 || p.s2 != cmd.s2 || p.bell != (bell != nullptr)) {
+      if (!p.exec || p.gen != ctx->tune_gen || (is_dot && p.timeout_gen != p2p_timeout_gen()) || p.s0 != cmd.s0 || p.s1 != cmd.s1 || p.s2 != cmd.s2 || p.bell != (bell != nullptr)) {
         if (int rc = build_plan(ctx, s, cmd, bell, &p)) return rc;
       }
       B200_CUDA(cudaGraphLaunch(p.exec, s->stream));
@@ -355,6 +360,7 @@ static int shard_execute(b200_ctx* ctx, int g, const Command& cmd) {
     } else if (int rc = shard_launch(ctx, s, cmd, bell)) {
       return rc;
     }
+    if (is_dot && launches) s->dot_bell_seq = want;
     if (ctx->hostprof) t2 = clk::now();
     if (nccl_dot) {
       // the one collective of the whole benchmark: G partial sums -> every GPU holds the total
@@ -552,24 +558,38 @@ static int run_all(b200_ctx* ctx, const Command& cmd) {
   return rc;
 }
 
-static void parse_cfg_fields(b200_launch_cfg* c, const std::string& fields) {
+static int parse_cfg_fields(b200_launch_cfg* c, const std::string& fields) {
   // "vec=32,unroll=2,block=256,grid=-4,hint=3,variant=2,stages=4,chunk=32768,contract=1"
+  // Strict: an unknown field name or a value that is not a whole number is an error, not a silent "auto".
   size_t pos = 0;
   while (pos < fields.size()) {
     size_t end = fields.find(',', pos);
     if (end == std::string::npos) end = fields.size();
     const std::string kv = fields.substr(pos, end - pos);
-    const size_t eq = kv.find('=');
-    if (eq != std::string::npos) {
-      const std::string k = kv.substr(0, eq);
-      const int v = atoi(kv.c_str() + eq + 1);
-      if (k == "vec") c->vec_bytes = v; else if (k == "unroll") c->unroll = v; else if (k == "block") c->block = v;
-      else if (k == "grid") c->grid = v; else if (k == "hint") c->cache_hint = v; else if (k == "variant") c->variant = v;
-      else if (k == "stages") c->stages = v; else if (k == "chunk") c->chunk_bytes = v; else if (k == "contract") c->contract = v;
-      else if (k == "keep") c->keep_mb = v; else if (k == "flags") c->flags = v;
-    }
     pos = end + 1;
+    if (kv.empty()) continue;
+    const size_t eq = kv.find('=');
+    if (eq == std::string::npos || eq == 0) { set_error("tune: '%s' is not field=value", kv.c_str()); return B200_EINVAL; }
+    const std::string k = kv.substr(0, eq);
+    const char* text = kv.c_str() + eq + 1;
+    char* stop = nullptr;
+    errno = 0;
+    const long lv = strtol(text, &stop, 10);
+    if (stop == text || *stop != '\0' || errno == ERANGE || lv < INT_MIN || lv > INT_MAX) {
+      set_error("tune: value of '%s' is not an integer: '%s'", k.c_str(), text);
+      return B200_EINVAL;
+    }
+    const int v = (int)lv;
+    if (k == "vec") c->vec_bytes = v; else if (k == "unroll") c->unroll = v; else if (k == "block") c->block = v;
+    else if (k == "grid") c->grid = v; else if (k == "hint") c->cache_hint = v; else if (k == "variant") c->variant = v;
+    else if (k == "stages") c->stages = v; else if (k == "chunk") c->chunk_bytes = v; else if (k == "contract") c->contract = v;
+    else if (k == "keep") c->keep_mb = v; else if (k == "flags") c->flags = v;
+    else {
+      set_error("tune: unknown field '%s' (fields: vec unroll block grid hint variant stages chunk contract keep flags)", k.c_str());
+      return B200_EINVAL;
+    }
   }
+  return B200_OK;
 }
 
 static int kernel_by_name(const std::string& s) {
@@ -592,17 +612,33 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
     if (val != "graph" && val != "direct") { set_error("launch must be graph or direct, got '%s'", val.c_str()); return B200_EINVAL; }
     ctx->use_graphs = val == "graph";
   } else if (key == "contract") {
-    const int c = (val == "off" || val == "0" || val == "unfused") ? 2 : 1;
-    for (auto& t : ctx->tune) t.contract = c;
+    const bool off = val == "off" || val == "0" || val == "unfused";
+    if (!off && val != "fast" && val != "1" && val != "fused" && val != "on") {
+      set_error("contract must be fast (fused, on, 1) or off (unfused, 0), got '%s'", val.c_str()); return B200_EINVAL;
+    }
+    for (auto& t : ctx->tune) t.contract = off ? 2 : 1;
   } else if (key == "copy_variant") {
+    if (val != "auto" && val != "ldst" && val != "bulk" && val != "tma") {
+      set_error("copy_variant must be auto, ldst, bulk or tma, got '%s'", val.c_str()); return B200_EINVAL;
+    }
     int v = val == "ldst" ? B200_VARIANT_LDST : val == "bulk" ? B200_VARIANT_BULK : val == "tma" ? B200_VARIANT_TMA : B200_VARIANT_AUTO;
     ctx->tune[B200_COPY].variant = v;
   } else if (key == "dot_variant") {
+    if (val != "auto" && val != "two_pass" && val != "ticket") {
+      set_error("dot_variant must be auto, two_pass or ticket, got '%s'", val.c_str()); return B200_EINVAL;
+    }
     ctx->tune[B200_DOT].variant = val == "two_pass" ? B200_VARIANT_DOT_TWO_PASS : val == "ticket" ? B200_VARIANT_DOT_TICKET : 0;
   } else if (key == "dot_combine") {
+    if (val != "auto" && val != "host" && val != "p2p" && val != "nccl") {
+      set_error("dot_combine must be auto, host, p2p or nccl, got '%s'", val.c_str()); return B200_EINVAL;
+    }
     ctx->combine = val == "host" ? COMBINE_HOST : val == "p2p" ? COMBINE_P2P : val == "nccl" ? COMBINE_NCCL : COMBINE_AUTO;
   } else if (key == "timing") {
-    ctx->timing = (val == "1" || val == "on" || val == "true");
+    const bool on = val == "1" || val == "on" || val == "true";
+    if (!on && val != "0" && val != "off" && val != "false") {
+      set_error("timing must be 0 (off, false) or 1 (on, true), got '%s'", val.c_str()); return B200_EINVAL;
+    }
+    ctx->timing = on;
   } else if (key == "mem") {
     const bool pf = val == "pagefault";
     const bool want = val == "managed" || pf;
@@ -614,26 +650,49 @@ static int apply_option(b200_ctx* ctx, const std::string& key, const std::string
     ctx->managed = want;
     ctx->pagefault = pf;
   } else if (key == "sync") {
+    if (val != "auto" && val != "stream" && val != "spin" && val != "doorbell") {
+      set_error("sync must be auto, stream, spin or doorbell, got '%s'", val.c_str()); return B200_EINVAL;
+    }
     ctx->sync_mode = val == "spin" ? SYNC_SPIN : val == "stream" ? SYNC_STREAM : val == "doorbell" ? SYNC_DOORBELL : SYNC_AUTO;
   } else if (key == "tune") {
-    // "<kernel>:<fields>;<kernel>:<fields>"   kernel "all" applies to the six elementwise kernels
+    // "<kernel>:<fields>;<kernel>:<fields>"   kernel "all" applies to the six elementwise kernels.
+    // Parsed into a copy, checked as a launch would check it, and only then adopted: a bad shape fails HERE, not at
+    // the first call that uses it (a failed dot launch used to leave the doorbell count one short for good).
+    b200_launch_cfg next[B200_NUM_KERNELS];
+    memcpy(next, ctx->tune, sizeof next);
+    bool touched[B200_NUM_KERNELS] = {};
     size_t pos = 0;
     while (pos < val.size()) {
       size_t end = val.find(';', pos);
       if (end == std::string::npos) end = val.size();
       const std::string item = val.substr(pos, end - pos);
-      const size_t colon = item.find(':');
-      if (colon != std::string::npos) {
-        const std::string kn = item.substr(0, colon), fields = item.substr(colon + 1);
-        if (kn == "all") { for (int k = 0; k < B200_NUM_KERNELS; k++) if (k != B200_DOT) parse_cfg_fields(&ctx->tune[k], fields); }
-        else {
-          const int k = kernel_by_name(kn);
-          if (k < 0) { set_error("tune: unknown kernel '%s'", kn.c_str()); return B200_EINVAL; }
-          parse_cfg_fields(&ctx->tune[k], fields);
-        }
-      }
       pos = end + 1;
+      if (item.empty()) continue;
+      const size_t colon = item.find(':');
+      if (colon == std::string::npos) { set_error("tune: '%s' is not <kernel>:<field>=<v>,...", item.c_str()); return B200_EINVAL; }
+      const std::string kn = item.substr(0, colon), fields = item.substr(colon + 1);
+      if (kn == "all") {
+        for (int k = 0; k < B200_NUM_KERNELS; k++)
+          if (k != B200_DOT) { if (int rc = parse_cfg_fields(&next[k], fields)) return rc; touched[k] = true; }
+      } else {
+        const int k = kernel_by_name(kn);
+        if (k < 0) { set_error("tune: unknown kernel '%s'", kn.c_str()); return B200_EINVAL; }
+        if (int rc = parse_cfg_fields(&next[k], fields)) return rc;
+        touched[k] = true;
+      }
     }
+    const size_t per_gpu = ctx->ngpus > 0 ? (ctx->n + (size_t)ctx->ngpus - 1) / (size_t)ctx->ngpus : ctx->n;
+    for (int k = 0; k < B200_NUM_KERNELS; k++) {
+      if (!touched[k]) continue;
+      b200_sweep_plan plan;
+      if (b200_plan_sweep(k, per_gpu, ctx->elem_bytes, 148, 126 << 20, &next[k], &plan)) {
+        const std::string why = b200_last_error();
+        const char* names[B200_NUM_KERNELS] = {"copy", "mul", "add", "triad", "nstream", "dot", "init"};
+        set_error("tune: %s: %s", names[k], why.c_str());
+        return B200_EINVAL;
+      }
+    }
+    memcpy(ctx->tune, next, sizeof next);
   } else {
     set_error("unknown option '%s'", key.c_str());
     return B200_EINVAL;

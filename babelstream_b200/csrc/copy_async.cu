@@ -61,8 +61,8 @@ int launch_copy_bulk(const void* src, void* dst, size_t bytes, const Resolved& r
   args.evict_first = (r.cache_hint == B200_HINT_EVICT_FIRST || r.cache_hint == B200_HINT_STREAM) ? 1 : 0;
   const unsigned grid = grid_for(r.grid_policy == INT32_MAX ? -1 : r.grid_policy, args.nchunks ? args.nchunks : 1, props.num_sms);
   copy_bulk_kernel<<<grid, 128, smem, stream>>>(args);
-  count_launch();
   B200_CUDA(cudaPeekAtLastError());
+  count_launch();
   return B200_OK;
 }
 
@@ -144,8 +144,8 @@ int launch_copy_tma(const void* src, void* dst, size_t bytes, const Resolved& r,
   }
   const unsigned grid = grid_for(r.grid_policy == INT32_MAX ? -1 : r.grid_policy, args.nchunks ? args.nchunks : 1, props.num_sms);
   copy_tma_kernel<<<grid, 128, smem, stream>>>(args, src_map, dst_map, rows_per_chunk);
-  count_launch();
   B200_CUDA(cudaPeekAtLastError());
+  count_launch();
   return B200_OK;
 }
 

@@ -1,6 +1,8 @@
 // dot.cu -- launcher for the two dot variants (see kernels.cuh for the algorithm).
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "internal.h"
 #include "kernels.cuh"
 
@@ -8,16 +10,25 @@ namespace b200 {
 
 // How long the collecting warp of the peer-memory all-reduce waits for a missing peer before it gives up
 // and reports B200_ETIMEOUT: BABELSTREAM_B200_P2P_TIMEOUT_MS (default 2000), b200_set_p2p_timeout_ms().
-static unsigned long long g_p2p_timeout_ns = 0;
+// 0 = not read from the environment yet.  Atomics: the worker threads of a multi-GPU context read it concurrently.
+static std::atomic<unsigned long long> g_p2p_timeout_ns{0};
+static std::atomic<unsigned long long> g_p2p_timeout_gen{1};  // bumped by every change: captured dot plans carry the value
 unsigned long long p2p_timeout_ns() {
-  if (g_p2p_timeout_ns == 0) {
+  unsigned long long ns = g_p2p_timeout_ns.load(std::memory_order_acquire);
+  if (ns == 0) {
     double ms = 2000.0;
     if (const char* e = getenv("BABELSTREAM_B200_P2P_TIMEOUT_MS")) { const double v = atof(e); if (v > 0) ms = v; }
-    g_p2p_timeout_ns = (unsigned long long)(ms * 1e6);
+    unsigned long long expected = 0;
+    ns = (unsigned long long)(ms * 1e6);
+    if (!g_p2p_timeout_ns.compare_exchange_strong(expected, ns, std::memory_order_acq_rel)) ns = expected;  // someone set it meanwhile
   }
-  return g_p2p_timeout_ns;
+  return ns;
 }
-void set_p2p_timeout_ns(unsigned long long ns) { g_p2p_timeout_ns = ns ? ns : 1; }
+void set_p2p_timeout_ns(unsigned long long ns) {
+  g_p2p_timeout_ns.store(ns ? ns : 1, std::memory_order_release);
+  g_p2p_timeout_gen.fetch_add(1, std::memory_order_acq_rel);
+}
+unsigned long long p2p_timeout_gen() { return g_p2p_timeout_gen.load(std::memory_order_acquire); }
 
 #define B200_DOT_FOR_HINT(H)                                                                      \
   B200_DOT_CASE(8, 1, H) B200_DOT_CASE(8, 2, H) B200_DOT_CASE(8, 4, H)                            \

@@ -32,8 +32,10 @@ void count_launch(unsigned n = 1);
 void uncount_launch(unsigned n);   // a stream capture "launched" n kernels that never ran
 uint64_t thread_launch_count();    // launches counted on the calling thread
 
-// Every kernel of the library is launched through here.  flags & B200_LAUNCH_PDL adds the
-// programmatic-stream-serialization attribute (see pdl_entry() in kernels.cuh).
+// Every register-path kernel (elementwise, dot, collect) is launched through here.  flags & B200_LAUNCH_PDL adds the
+// programmatic-stream-serialization attribute (see pdl_entry() in kernels.cuh).  The two async-proxy copy variants
+// (copy_async.cu) launch with <<<>>> and have no dependent-launch entry: for them B200_LAUNCH_PDL has no effect (a plain
+// launch is fully stream-ordered, the stronger guarantee).
 template <typename... KArgs, typename... Args>
 int launch_kernel(void (*kernel)(KArgs...), unsigned grid, int block, size_t smem, cudaStream_t stream, int flags,
                   Args&&... args) {
@@ -50,14 +52,15 @@ int launch_kernel(void (*kernel)(KArgs...), unsigned grid, int block, size_t sme
     cfg.numAttrs = 1;
   }
   const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
-  count_launch();
   if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx", __FILE__, __LINE__);
+  count_launch();  // only what was really enqueued
   return B200_OK;
 }
 
 // bound of the peer-memory all-reduce's wait for a missing peer (dot.cu)
 unsigned long long p2p_timeout_ns();
 void set_p2p_timeout_ns(unsigned long long ns);
+unsigned long long p2p_timeout_gen();  // changes whenever the bound does (a captured dot launch has the bound baked in)
 
 // A fully resolved launch: no "auto" left.
 struct Resolved {

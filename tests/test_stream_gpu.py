@@ -366,6 +366,49 @@ def test_constructor_errors():
         bs.B200Stream(16, dtype=np.int32)
 
 
+def test_bad_option_values_are_refused_not_mapped_to_auto(orc):
+    """A benchmark that silently runs another configuration than the one asked for prints wrong tables: every
+    misspelt value is B200_EINVAL with the accepted list (the reference refuses unknown flags, src/main.cpp:423-603)."""
+    n = 1 << 16
+    with bs.B200Stream(n, dtype=np.float64) as s:
+        before = s.describe()
+        for key, bad, word in (("copy_variant", "tmaa", "ldst"), ("dot_variant", "tickets", "two_pass"),
+                               ("dot_combine", "ncl", "nccl"), ("sync", "doorbel", "doorbell"), ("contract", "fats", "off"),
+                               ("timing", "yes", "off"), ("sweep", "alt", "forward"), ("launch", "graphs", "direct"),
+                               ("tune", "triad:vec=16,unrol=4", "unknown field"), ("tune", "triad:vec=1x6", "not an integer"),
+                               ("tune", "triad:vec", "field=value"), ("tune", "tirad:vec=16", "unknown kernel"),
+                               ("tune", "triad:vec=24", "vec_bytes"), ("tune", "dot:block=1024", "block"),
+                               ("tune", "triad", "<kernel>:"), ("nosuchkey", "1", "unknown option")):
+            with pytest.raises(bs.B200Error) as e:
+                s.set_option(key, bad)
+            assert word in str(e.value), (key, bad, str(e.value))
+        assert s.describe() == before, "a refused option must leave the configuration as it was"
+        total = drive(s, orc, O.ALL, O.ORDER_CLASSIC, 2)
+        a, b, c = s.get_arrays()
+        assert orc.check_solution(O.ALL, O.ORDER_CLASSIC, 2, a, b, c, total) == 0
+    with pytest.raises(bs.B200Error, match="copy_variant must be"):
+        bs.B200Stream(n, dtype=np.float64, copy_variant="tmaa")
+
+
+def test_dot_survives_a_refused_tune(orc):
+    """a dot shape the launcher would refuse (block 1024, a grid beyond the workspace) used to be accepted by
+    set_option and to fail at the next dot, after which the host waited for a doorbell value the device never reached.
+    Such shapes now fail at set time and leave the context as it was; the host's doorbell count also follows the
+    device's only when a launch went through."""
+    n = 1 << 18
+    with bs.B200Stream(n, dtype=np.float64) as s:
+        s.init_arrays()
+        good = s.dot()
+        for bad in ("dot:block=1024", "dot:hint=9", "dot:vec=32,unroll=8"):
+            with pytest.raises(bs.B200Error):
+                s.set_option("tune", bad)
+            assert bits(np.float64(s.dot())) == bits(np.float64(good)), bad
+        s.set_option("tune", "dot:vec=16,unroll=2,block=256")  # a legal one still goes through, and dot keeps working
+        for _ in range(3):
+            got = s.dot()
+            assert abs(float(got) - float(good)) <= 64 * np.finfo(np.float64).eps * abs(float(good))
+
+
 needs_bin = pytest.mark.skipif(not os.path.exists(BIN), reason="build/b200-stream not built (needs the reference tree)")
 
 
@@ -456,6 +499,12 @@ def test_driver_list_and_bad_device():
     assert p.returncode == 0 and "0:" in p.stdout
     p = run_bin("--device", "99", "-s", "1024", "-n", "2")
     assert p.returncode != 0 and "Invalid device index" in p.stderr
+
+
+@needs_bin
+def test_driver_refuses_a_misspelt_option():
+    p = run_bin("-s", "65536", "-n", "2", env={"BABELSTREAM_B200_COPY_VARIANT": "tmaa"})
+    assert p.returncode != 0 and "copy_variant must be" in (p.stderr + p.stdout), p.stdout + p.stderr
 
 
 multi = pytest.mark.skipif(bs.lib() is None or bs.device_count() < 2, reason="needs >= 2 GPUs")
