@@ -1,15 +1,9 @@
 #!/bin/bash
-# Round 2, GPU session I (1 GPU; compute-sanitizer is the only tool of this call): memcheck/racecheck on ragged sizes,
-# dot grid multiples of the resident block count, the fp32 rows of the per-size table, both bench arms.
+# Round 2, GPU session I (1 GPU): dot grid multiples of the resident block count, the fp32 rows of the per-size table, both bench arms.
 set -u
 O=gpurun_out/r2i
 mkdir -p $O
 drv() { "$1" --csv --gigabytes -s $2 --only $3 -n $4 "${@:5}" 2>/dev/null | grep -E "^(Copy|Mul|Add|Triad|Dot|Nstream)," | cut -d, -f1,6 | awk -F, '{printf "%s %.2f  ", $1, $2*1e6; s+=$2*1e6} END {printf "sum %.2f", s}'; }
-echo "== compute-sanitizer"
-for tool in memcheck racecheck; do
-  timeout 240 compute-sanitizer --tool $tool --error-exitcode 9 ./build/b200-stream -s 100003 -n 3 --only All > $O/sanitizer_${tool}_driver.log 2>&1; echo "$tool driver rc=$?"; tail -4 $O/sanitizer_${tool}_driver.log
-done
-timeout 300 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest tests/test_kernels_gpu.py -m gpu -q -x -k "ragged or misaligned or edge or small" > $O/sanitizer_memcheck_pytest.log 2>&1; echo "memcheck pytest rc=$?"; tail -5 $O/sanitizer_memcheck_pytest.log
 echo "== dot grids at 2^25 (min us, --only All)" | tee $O/dot_grids.txt
 for cfg in "" "dot:grid=-3" "dot:grid=-6" "dot:grid=-9" "dot:grid=-12" "dot:grid=-15" "dot:block=256,grid=-6" "dot:block=256,grid=-12" "dot:block=256,grid=-18"; do
   echo "2^25 [$cfg]: $(BABELSTREAM_B200_TUNE="$cfg" drv build/b200-stream 33554432 All 100)" | tee -a $O/dot_grids.txt
