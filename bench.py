@@ -82,6 +82,9 @@ def make_config(log2n: int, world: int) -> dict:
             "parallelism": "1 GPU" if world == 1 else
                            f"{world} ranks (one process per GPU), contiguous shards, no collective for the elementwise kernels, "
                            "dot partials combined by one exchange step",
+            "dot_combine": "none (1 GPU)" if world == 1 else
+                           "p2p: peer-memory all-reduce over NVLink inside the dot kernel (nccl: one ncclAllReduce, when peer "
+                           "access is missing) -- the mode that ran is the line's top-level dot_combine",
             "timing": "CUDA events on the launching stream, max over ranks"}
 
 
@@ -277,6 +280,10 @@ def main_reference(args, rank, world):
             "steps": K, "warmup": W, "ms_per_step": round(t * 1e3, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": make_config(args.log2n, args.gpus),
+            "elements_run": n,
+            "elements_run_note": f"this arm runs 2^{args.log2n} elements on the host whatever --gpus says; config.elements_total "
+                                 f"({n * args.gpus}) is the GPU arm's job at N = {args.gpus}, repeated here so that the two lines "
+                                 "carry the same config",
             "run_as": "the reference's OpenMP model on the host CPU cores (no GPU); each step is a bounded sample of the "
                       f"workload: one pass of the six kernels over 2^{args.log2n} fp64 elements, whatever --gpus says",
             "cpu_baseline": base,
@@ -533,6 +540,14 @@ def main():
     launches = bs.launch_count() - launches0
     total_ms = ev_a0.elapsed_time(ev_a1)
     dot_value = float(dot_out.item())
+    # the region behind `value` proves itself: its a, b, c after the K timed steps against the gold recurrence, bit for
+    # bit, and its last all-rank dot -- outside the timed region, before region B re-initialises the arrays
+    ra_gold = gold_recurrence(K)
+    ra_bits = [int(np.asarray([g], dtype=np.float64).view(np.int64)[0]) for g in ra_gold[:3]]
+    ra_wrong = sum(int((x.view(torch.int64) != gbits).sum().item()) for x, gbits in zip((a, b, c), ra_bits))
+    ra_sum = ra_gold[3] * ra_gold[4] * float(n * world)
+    ra_rel = abs(dot_value - ra_sum) / max(abs(dot_value), abs(ra_sum))
+    ra_dot_ok = bool(np.isfinite(dot_value)) and ra_rel <= 1e7 * float(np.finfo(np.float64).eps)
     barrier()
 
     # ---- device-timed region B: an event at every kernel boundary (per-kernel GB/s, roofline) ---------
@@ -600,11 +615,19 @@ def main():
     gold_sum = a_dot * b_dot * float(n * world)          # src/main.cpp:349
     dot_rel = abs(float(e2e_v) - gold_sum) / max(abs(float(e2e_v)), abs(gold_sum))
     dot_ok = dot_rel <= 1e7 * np.finfo(np.float64).eps and np.isfinite(float(e2e_v))   # src/main.cpp:384
-    pt = torch.tensor([float(wrong), 0.0 if dot_ok else 1.0, dot_rel], dtype=torch.float64, device="cuda")
+    pt = torch.tensor([float(wrong), 0.0 if dot_ok else 1.0, dot_rel, float(ra_wrong), 0.0 if ra_dot_ok else 1.0, ra_rel],
+                      dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(pt, op=dist.ReduceOp.MAX)
     pt = pt.cpu().tolist()
-    parity = {"ok": pt[0] == 0 and pt[1] == 0, "array_elements_differing_from_gold_bits_max_over_ranks": int(pt[0]),
+    parity = {"ok": pt[0] == 0 and pt[1] == 0 and pt[3] == 0 and pt[4] == 0,
+              "value_region": {"ok": pt[3] == 0 and pt[4] == 0,
+                               "array_elements_differing_from_gold_bits_max_over_ranks": int(pt[3]),
+                               "dot": dot_value, "dot_gold": ra_sum, "dot_rel_err_max_over_ranks": pt[5],
+                               "how": "the device-timed region A itself (asynchronous launches, dependent launch, split "
+                                      "send/collect dot at N > 1): its a, b, c after the K timed steps bit for bit against the "
+                                      "gold recurrence and its last all-rank dot within 1e7*eps, checked before the arrays are "
+                                      "re-initialised"}, "array_elements_differing_from_gold_bits_max_over_ranks": int(pt[0]),
               "arrays_checked_per_rank": 3 * n, "steps": K,
               "gold_bits": {"a": "0x%016x" % u64(gold_a), "b": "0x%016x" % u64(gold_b), "c": "0x%016x" % u64(gold_c)},
               "dot": float(e2e_v), "dot_gold": gold_sum, "dot_rel_err_max_over_ranks": pt[2], "dot_bound": 1e7 * float(np.finfo(np.float64).eps),
