@@ -191,19 +191,46 @@ class _start_affinity:
         return False
 
 
-def run_stream_binary(path, n, num_times, only="All", env=None, timeout=900, want_wall=False):
+def run_stream_binary(path, n, num_times, only="All", env=None, timeout=900, want_wall=False, extra_args=()):
     """Runs a BabelStream binary (ours or a reference model); a non-zero exit (check_solution failed) raises."""
     e = dict(os.environ)
     e.update(env or {})
     t0 = time.perf_counter()
     with _start_affinity():
-        p = subprocess.run([path, "--csv", "--gigabytes", "-s", str(n), "-n", str(num_times), "--only", only],
+        p = subprocess.run([path, "--csv", "--gigabytes", "-s", str(n), "-n", str(num_times), "--only", only, *extra_args],
                            capture_output=True, text=True, timeout=timeout, env=e)
     wall = time.perf_counter() - t0
     if p.returncode != 0:
         raise RuntimeError(f"{os.path.basename(path)} exited {p.returncode}: {p.stderr[-400:]}")
     rows = parse_stream_csv(p.stdout)
     return (rows, wall) if want_wall else rows
+
+
+def config3_size_sweep(binaries, l2_bytes=126 << 20):
+    """BASELINE config 3: fp32 and fp64, 2^20 ... 2^30 elements, --only All through the unmodified driver (its own clock,
+    min time per kernel as it prints it), for each binary in `binaries` ({label: path}).  Every row says whether the three
+    arrays fit the L2 (the knee between the L2-resident and the HBM-bound regime)."""
+    rows = []
+    for log2n in (20, 22, 24, 26, 28, 30):
+        n = 1 << log2n
+        for dt, eb, flag in (("f64", 8, ()), ("f32", 4, ("--float",))):
+            foot = 3 * n * eb
+            row = {"log2n": log2n, "dtype": dt, "footprint_mb": round(foot / 1e6, 1),
+                   "regime": "L2-resident" if foot <= l2_bytes else ("knee" if foot <= 4 * l2_bytes else "HBM")}
+            num_times = 100 if log2n <= 26 else 30 if log2n <= 28 else 10
+            for label, path in binaries.items():
+                try:
+                    r = run_stream_binary(path, n, num_times, extra_args=flag)   # non-zero exit = check_solution failed
+                    t = sum(r[k]["min_s"] for k in KERNEL_ORDER)
+                    row[label] = {"step_gbs": round(STEP_WEIGHT * eb * n / t / 1e9, 1), "triad_gbs": round(r["triad"]["gbs"], 1),
+                                  "dot_gbs": round(r["dot"]["gbs"], 1), "copy_gbs": round(r["copy"]["gbs"], 1)}
+                except Exception as e:  # noqa: BLE001
+                    row[label] = {"error": str(e)[:160]}
+            rows.append(row)
+    return {"what": "BASELINE config 3 through the unmodified driver: --only All, min time per kernel (src/main.cpp clock), "
+                    "check_solution passed in every run that reports a figure; step_gbs = bytes of the six kernels / sum of their "
+                    "min times; -n 100 up to 2^26, 30 at 2^28, 10 at 2^30",
+            "l2_mb": round(l2_bytes / 1e6, 1), "rows": rows}
 
 
 def step_gbs_from_csv(rows, n, key="avg_s"):
@@ -380,6 +407,24 @@ def strong_scaling(world, rank, local, dist, cpu_group, no_extras):
                 rows = run_stream_binary(b200_bin, 1 << 31, 20, only="All", env={"BABELSTREAM_B200_NGPUS": "8"}, timeout=1200)
                 drv["all_2^31"] = {k: round(v["gbs"], 1) for k, v in rows.items()}
                 drv["all_2^31"]["check_solution"] = "passed"
+            if world > 1:
+                # BASELINE config 5's "one NCCL allreduce over NVLink", next to the two other ways the in-process model can
+                # combine the G partial sums; --only Dot, the driver's clock, check_solution decides the exit code
+                combos = {}
+                for nd, label in ((world << 25, f"2^25 x {world}"),) + (((1 << 31, "2^31"),) if world == 8 else ()):
+                    per_mode = {}
+                    for mode in ("host", "p2p", "nccl"):
+                        try:
+                            rows = run_stream_binary(b200_bin, nd, 100, only="Dot", timeout=600,
+                                                     env={"BABELSTREAM_B200_NGPUS": str(world), "BABELSTREAM_B200_DOT_COMBINE": mode})
+                            per_mode[mode] = {"gbs": round(rows["dot"]["gbs"], 1), "check_solution": "passed"}
+                        except Exception as e:  # noqa: BLE001
+                            per_mode[mode] = {"error": str(e)[:200]}
+                    combos[label] = per_mode
+                combos["how"] = (f"BABELSTREAM_B200_NGPUS={world} BABELSTREAM_B200_DOT_COMBINE=host|p2p|nccl build/b200-stream --only Dot "
+                                 "-n 100: host = rank-order sum of the G doorbell-delivered partials on the caller's thread, p2p = "
+                                 "all-reduce over peer memory inside the dot kernel, nccl = dot kernel + one ncclAllReduce per call")
+                drv["dot_combine"] = combos
         except Exception as e:  # noqa: BLE001
             drv["error"] = str(e)[:300]
         drv["how"] = (f"BABELSTREAM_B200_NGPUS={world} build/b200-stream -s 2^30 -n 20 --only Triad|Nstream (the reference's "
@@ -813,6 +858,9 @@ def main():
                         ns["reference_thrust_stream_driver_gbs"] = round(r3["triad"]["gbs"], 1)
                     line["roofline"]["north_star"] = ns
                     extras["north_star_triad_2^29"] = ns
+                bins = {k: v for k, v in (("b200_stream", b200_bin), ("reference_cuda_stream", cuda_bin)) if os.path.exists(v)}
+                if "b200_stream" in bins:
+                    extras["config3_size_sweep"] = config3_size_sweep(bins)
             except Exception as e:  # noqa: BLE001
                 extras["error"] = str(e)[:300]
             line["driver"] = extras
