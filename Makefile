@@ -28,7 +28,7 @@ SRCS := $(wildcard $(CSRC)/*.cu)
 OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(SRCS))
 HDRS := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) include/b200_stream.h
 
-.PHONY: all lib driver oracle clean ptxas probe lab
+.PHONY: all lib driver oracle clean ptxas probe lab sass
 all: lib oracle driver
 
 lib: $(LIB)
@@ -77,6 +77,12 @@ build/latency_probe: tools/latency_probe.cu $(LIB) include/b200_stream.h
 
 ptxas:
 	@cat $(OBJDIR)/*.ptxas.log | grep -E "Compiling|registers|spill" | paste - - - | sort | uniq | head -2000
+
+# opcode histograms of the default-selected kernels (and the async-proxy copy variants): the committed SASS evidence
+sass: lib
+	@mkdir -p profiles/r03
+	python tools/sass_summary.py > profiles/r03/sass_summary.txt
+	@echo wrote profiles/r03/sass_summary.txt
 
 clean:
 	rm -rf build $(LIB)
