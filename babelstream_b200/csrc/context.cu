@@ -592,6 +592,24 @@ static int parse_cfg_fields(b200_launch_cfg* c, const std::string& fields) {
   return B200_OK;
 }
 
+// Does the calling thread have a CUDA context current?  Asked of the driver (cuCtxGetCurrent, fetched through the runtime:
+// no link-time dependency on libcuda) because every runtime call that could tell would create one.
+static bool thread_has_cuda_context() {
+  using GetCurrentFn = int (*)(void**);
+  static GetCurrentFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuCtxGetCurrent", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      p = nullptr;
+    }
+    return reinterpret_cast<GetCurrentFn>(p);
+  }();
+  if (!fn) return true;  // cannot tell: behave as before (restore the caller's device)
+  void* cur = nullptr;
+  return fn(&cur) == 0 && cur != nullptr;
+}
+
 static int kernel_by_name(const std::string& s) {
   const char* names[B200_NUM_KERNELS] = {"copy", "mul", "add", "triad", "nstream", "dot", "init"};
   for (int i = 0; i < B200_NUM_KERNELS; i++) if (s == names[i]) return i;
@@ -859,6 +877,12 @@ b200_ctx* b200_create_opts(int first_device, int ngpus, size_t n, int elem_bytes
   ctx->first_device = first_device; ctx->ngpus = ngpus; ctx->n = n; ctx->elem_bytes = elem_bytes;
   memset(ctx->tune, 0, sizeof ctx->tune);
   if (cudaGetDevice(&ctx->caller_device) != cudaSuccess) { (void)cudaGetLastError(); ctx->caller_device = -1; }
+  // A caller that has never touched CUDA on this thread (the reference's driver: main.cpp only constructs the model) has
+  // no device of its own to go back to -- cudaGetDevice just says 0.  "Restoring" 0 would create a primary context on
+  // GPU 0 for `--device 1` (memory and start-up time on a GPU the run does not use) and make every later blocking call
+  // switch devices twice.  For such a caller the context's first device simply stays current, as the reference's
+  // constructor leaves it (CUDAStream.cu:89).
+  if (!thread_has_cuda_context()) ctx->caller_device = -1;
 
   // options from the environment: BABELSTREAM_B200_<KEY>
   const char* keys[] = {"contract", "copy_variant", "dot_variant", "dot_combine", "timing", "sync", "tune", "mem", "launch", "sweep", "pin"};
