@@ -144,6 +144,7 @@ struct b200_ctx {
   bool timing = false;
   bool created = false;  // b200_create finished: the allocation-time options are frozen
   int sync_mode = SYNC_AUTO;
+  std::vector<int> claimed_cpus;  // CPUs this context's workers were given (process-wide registry, see choose_worker_cpus)
   int caller_device = -1;    // the device that was current when b200_create was called; restored by create and destroy
   bool use_graphs = true;    // option launch=graph|direct
   bool pin = true;           // option pin=auto|off: pin every worker thread to a core of its own near its GPU
@@ -462,7 +463,23 @@ static long core_key(int cpu) {
   return pkg * 100000 + core;
 }
 
+// CPUs handed to worker threads by ANY context of this process: two multi-GPU contexts side by side must not stack
+// their spinning workers on the same cores while others idle.  Released in b200_destroy.  (Separate PROCESSES cannot
+// see each other's choice: give them disjoint taskset masks, or pin=off.)
+static std::mutex g_pin_mutex;
+static std::vector<int> g_pinned_cpus;
+
+static void release_worker_cpus(b200_ctx* ctx) {
+  std::lock_guard<std::mutex> lock(g_pin_mutex);
+  for (int c : ctx->claimed_cpus) {
+    for (size_t i = 0; i < g_pinned_cpus.size(); i++)
+      if (g_pinned_cpus[i] == c) { g_pinned_cpus.erase(g_pinned_cpus.begin() + (long)i); break; }
+  }
+  ctx->claimed_cpus.clear();
+}
+
 static void choose_worker_cpus(b200_ctx* ctx) {
+  std::lock_guard<std::mutex> lock(g_pin_mutex);
   cpu_set_t allowed;
   CPU_ZERO(&allowed);
   if (sched_getaffinity(0, sizeof allowed, &allowed) != 0) return;
@@ -471,6 +488,7 @@ static void choose_worker_cpus(b200_ctx* ctx) {
   std::vector<int> used_cpus;
   const int here = sched_getcpu();
   if (here >= 0) { used_cores.push_back(core_key(here)); used_cpus.push_back(here); }
+  for (int c : g_pinned_cpus) { used_cores.push_back(core_key(c)); used_cpus.push_back(c); }  // other contexts' workers
   auto is_in = [](const auto& v, auto x) { for (auto y : v) if (y == x) return true; return false; };
   for (int g = 1; g < ctx->ngpus; g++) {
     Shard* s = ctx->shards[g];
@@ -498,7 +516,10 @@ static void choose_worker_cpus(b200_ctx* ctx) {
       }
     }
     s->pin_cpu = pick;
-    if (pick >= 0) { used_cpus.push_back(pick); used_cores.push_back(core_key(pick)); }
+    if (pick >= 0) {
+      used_cpus.push_back(pick); used_cores.push_back(core_key(pick));
+      g_pinned_cpus.push_back(pick); ctx->claimed_cpus.push_back(pick);
+    }
   }
 }
 
@@ -823,6 +844,7 @@ void b200_destroy(b200_ctx* ctx) {
     ctx->cv.notify_all();
     for (auto& t : ctx->workers) t.join();
   }
+  release_worker_cpus(ctx);
   for (Shard* s : ctx->shards) {
     if (!s) continue;
     cudaSetDevice(s->dev);

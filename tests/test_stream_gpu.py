@@ -564,6 +564,26 @@ def test_multi_gpu_threading_options(orc):
 
 
 @multi
+def test_two_contexts_do_not_share_worker_cpus():
+    """the worker threads of two multi-GPU contexts living side by side in one process are pinned to different
+    CPUs (a process-wide registry, released by destroy), instead of both contexts choosing the same cores."""
+    import re
+
+    def cpus(s):
+        return [int(c) for c in re.findall(r"\d+->cpu(\d+)", s.describe())]
+
+    n = 1 << 20
+    with bs.B200Stream(n, dtype=np.float64, ngpus=2) as s:
+        first = cpus(s)
+        with bs.B200Stream(n, dtype=np.float64, ngpus=2) as d:
+            second = cpus(d)
+            if first and second:   # pinning may be unavailable (fewer CPUs than threads, restricted affinity)
+                assert not set(first) & set(second), (first, second)
+        with bs.B200Stream(n, dtype=np.float64, ngpus=2) as e:   # d's CPUs were released
+            assert cpus(e) == second or not second
+
+
+@multi
 @pytest.mark.parametrize("combine", ["p2p", "host"])
 def test_multi_gpu_managed_memory(orc, combine):
     """mem=managed over several GPUs: one managed range per array, shards on 2 MiB boundaries."""
